@@ -1,0 +1,92 @@
+"""ctypes binding of csrc/libddp_b200.so (declarations in include/ddp_b200.h).
+
+There is no fallback: if the library is missing or a call fails, the caller gets an
+exception.  Nothing in this package computes the training step on the CPU.
+"""
+import ctypes
+import os
+
+from .build import LIB_PATH
+
+c_void_p, c_int, c_int32, c_int64, c_uint64 = ctypes.c_void_p, ctypes.c_int, ctypes.c_int32, ctypes.c_int64, ctypes.c_uint64
+c_float, c_double, c_char_p = ctypes.c_float, ctypes.c_double, ctypes.c_char_p
+
+MODE_FWD, MODE_GRAD, MODE_STEP = 0, 1, 2
+OPT_ADAM, OPT_SGD = 0, 1
+MAX_JOBS = 4
+TOY_HIDDEN, TOY_PARAMS = 10, 371
+
+
+class DdpB200Error(RuntimeError):
+    pass
+
+
+class OptState(ctypes.Structure):
+    _fields_ = [("step", ctypes.c_longlong), ("seq", ctypes.c_longlong),
+                ("beta1_pow", c_double), ("beta2_pow", c_double)]
+
+
+class ToyJob(ctypes.Structure):
+    _fields_ = [("params", c_void_p), ("grads", c_void_p), ("m", c_void_p), ("v", c_void_p),
+                ("state", c_void_p), ("loss_ring", c_void_p), ("x", c_void_p), ("y", c_void_p),
+                ("idx", c_void_p), ("out", c_void_p),
+                ("B", c_int32), ("mode", c_int32), ("opt", c_int32), ("loss_ring_n", c_int32),
+                ("idx_rows", c_int32), ("idx_stride", c_int32),
+                ("lr", c_double), ("beta1", c_double), ("beta2", c_double), ("eps", c_double),
+                ("momentum", c_double)]
+
+
+_SIGNATURES = {
+    "ddpb_version": (c_int, []),
+    "ddpb_last_error": (c_char_p, []),
+    "ddpb_device_info": (c_int, [c_int, c_void_p, c_void_p, c_void_p]),
+    "ddpb_randperm": (c_int, [c_uint64, c_int64, c_void_p]),
+    "ddpb_sampler_indices": (c_int64, [c_int64, c_int, c_int, c_int, c_uint64, c_uint64, c_int, c_void_p, c_int64]),
+    "ddpb_sampler_epochs_i32": (c_int, [c_int64, c_int, c_int, c_int, c_uint64, c_uint64, c_int, c_int, c_void_p, c_int64]),
+    "ddpb_host_gather": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p, c_void_p]),
+    "ddpb_gather_batch": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p, c_void_p, c_void_p]),
+    "ddpb_toy_step": (c_int, [c_void_p, c_int, c_void_p]),
+    "ddpb_fused_avg_adam": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_float,
+                                    c_double, c_double, c_double, c_double, c_int64, c_void_p]),
+    "ddpb_fused_avg_adam_dev": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_float,
+                                        c_double, c_double, c_double, c_double, c_void_p, c_int, c_void_p]),
+    "ddpb_fused_avg_sgd": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_float, c_double, c_double, c_int64, c_void_p]),
+    "ddpb_nccl_load": (c_int, [c_char_p]),
+    "ddpb_get_unique_id": (c_int, [c_void_p]),
+    "ddpb_comm_create": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p]),
+    "ddpb_comm_destroy": (c_int, [c_void_p]),
+    "ddpb_broadcast_f32": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_void_p]),
+    "ddpb_allreduce_sum_f32": (c_int, [c_void_p, c_void_p, c_int64, c_void_p]),
+    "ddpb_stream_sync": (c_int, [c_void_p]),
+    "ddpb_memcpy_h2d_async": (c_int, [c_void_p, c_void_p, c_int64, c_void_p]),
+    "ddpb_memcpy_d2h_async": (c_int, [c_void_p, c_void_p, c_int64, c_void_p]),
+}
+
+_lib = None
+
+
+def exported_symbols():
+    """Names every build of the library must export (checked by the CPU test-suite)."""
+    return sorted(_SIGNATURES)
+
+
+def lib():
+    """The loaded library; raises if it has not been built (no CPU fallback exists)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise DdpB200Error(
+                f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'`. "
+                "This package has no CPU or PyTorch fallback for the training step.")
+        handle = ctypes.CDLL(LIB_PATH)
+        for name, (restype, argtypes) in _SIGNATURES.items():
+            fn = getattr(handle, name)
+            fn.restype, fn.argtypes = restype, argtypes
+        _lib = handle
+    return _lib
+
+
+def check(rc, what=""):
+    if rc != 0:
+        msg = lib().ddpb_last_error().decode(errors="replace")
+        raise DdpB200Error(f"{what or 'libddp_b200'} failed (code {rc}): {msg}")

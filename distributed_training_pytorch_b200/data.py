@@ -1,0 +1,268 @@
+"""Sampler and loaders with the call shapes of demo.py:139-154.
+
+DistributedSampler reproduces torch.utils.data.DistributedSampler's index stream
+bit-exactly (native host code, csrc/sampler.cu).  DataLoader replaces the reference's
+per-sample __getitem__ + default_collate (0.29 ms per batch on the host, more than a whole
+GPU step) by one native gather from the dense dataset into pinned staging rows; batches
+come out as HostBatch objects whose .cuda() is one async H2D copy of the whole (x, y)
+block.  With device_resident=True (or DDPB_DEVICE_DATA=1) the dataset and the sampler's
+index rows live in HBM and a batch is just an index-row handle (no per-step copies).
+"""
+import ctypes
+import math
+import os
+
+import numpy as np
+import torch
+
+from . import _lib
+
+
+class DistributedSampler:
+    """Same constructor and semantics as torch.utils.data.DistributedSampler
+    (torch:utils/data/distributed.py:66-157); built at demo.py:144."""
+
+    def __init__(self, dataset, num_replicas=None, rank=None, shuffle=True, seed=0, drop_last=False):
+        if num_replicas is None or rank is None:
+            import torch.distributed as dist
+            if not dist.is_available() or not dist.is_initialized():
+                raise RuntimeError("Requires distributed package to be available")
+            num_replicas = dist.get_world_size() if num_replicas is None else num_replicas
+            rank = dist.get_rank() if rank is None else rank
+        if rank >= num_replicas or rank < 0:
+            raise ValueError(f"Invalid rank {rank}, rank should be in the interval [0, {num_replicas - 1}]")
+        self.dataset, self.num_replicas, self.rank = dataset, num_replicas, rank
+        self.epoch, self.drop_last, self.shuffle, self.seed = 0, drop_last, shuffle, seed
+        n = len(dataset)
+        if drop_last and n % num_replicas != 0:
+            self.num_samples = math.ceil((n - num_replicas) / num_replicas)
+        else:
+            self.num_samples = math.ceil(n / num_replicas)
+        self.total_size = self.num_samples * self.num_replicas
+
+    def indices(self, epoch=None):
+        """int64 numpy array of this rank's indices for `epoch` (default: the current one)."""
+        out = np.empty(self.num_samples, np.int64)
+        got = _lib.lib().ddpb_sampler_indices(len(self.dataset), self.num_replicas, self.rank, int(self.shuffle),
+                                              self.seed, self.epoch if epoch is None else epoch,
+                                              int(self.drop_last), out.ctypes.data, out.size)
+        if got != self.num_samples:
+            _lib.check(2, "ddpb_sampler_indices")
+        return out
+
+    def epochs_i32(self, epoch0, nepochs):
+        """[nepochs, num_samples] int32 index rows for consecutive epochs (device-resident path)."""
+        out = np.empty((nepochs, self.num_samples), np.int32)
+        _lib.check(_lib.lib().ddpb_sampler_epochs_i32(len(self.dataset), self.num_replicas, self.rank,
+                                                      int(self.shuffle), self.seed, epoch0, nepochs,
+                                                      int(self.drop_last), out.ctypes.data, self.num_samples),
+                   "ddpb_sampler_epochs_i32")
+        return out
+
+    def __iter__(self):
+        return iter(self.indices().tolist())
+
+    def __len__(self):
+        return self.num_samples
+
+    def set_epoch(self, epoch):
+        self.epoch = epoch
+
+
+class HostBatch:
+    """One half (data or target) of a staged batch in pinned host memory.
+
+    Quacks like the pinned tensor the reference's DataLoader yields: .cuda()/.to(device)
+    move it (one async copy for the whole (x, y) block on first use), .size()/.shape
+    describe it; any other attribute is looked up on the pinned tensor itself."""
+
+    __slots__ = ("_stage", "_which")
+
+    def __init__(self, stage, which):
+        self._stage, self._which = stage, which
+
+    @property
+    def tensor(self):
+        return self._stage.host[self._which]
+
+    def cuda(self, device=None, non_blocking=False):
+        return self._stage.to_device(device)[self._which]
+
+    def to(self, device=None, *args, **kwargs):
+        dev = torch.device(device) if device is not None and not isinstance(device, torch.dtype) else None
+        if dev is None or dev.type == "cpu":
+            return self.tensor
+        return self._stage.to_device(dev)[self._which]
+
+    def size(self, dim=None):
+        return self.tensor.size() if dim is None else self.tensor.size(dim)
+
+    @property
+    def shape(self):
+        return self.tensor.shape
+
+    def __len__(self):
+        return self.tensor.shape[0]
+
+    def __getattr__(self, name):
+        return getattr(self._stage.host[self._which], name)
+
+
+class _Stage:
+    """A pinned (x | y) block and its device twin; a DataLoader cycles through a few."""
+
+    def __init__(self, batch, dx, dy):
+        self.block = torch.empty(batch * (dx + dy), dtype=torch.float32, pin_memory=torch.cuda.is_available())
+        self.batch, self.dx, self.dy = batch, dx, dy
+        self._dev = {}         # device index -> (block, views by B)
+        self._copied_to = None
+        self.set_rows(batch)
+
+    def set_rows(self, B):
+        self.B = B
+        self.host = (self.block[:B * self.dx].view(B, self.dx),
+                     self.block[self.batch * self.dx:self.batch * self.dx + B * self.dy].view(B, self.dy))
+        self._copied_to = None
+
+    def to_device(self, device=None):
+        idx = torch.cuda.current_device() if device is None else torch.device(device).index
+        if idx is None:
+            idx = torch.cuda.current_device()
+        if self._copied_to is not None and self._copied_to[0] == idx:
+            return self._copied_to[1]
+        entry = self._dev.get(idx)
+        if entry is None:
+            entry = (torch.empty_like(self.block, device=f"cuda:{idx}"), {})
+            self._dev[idx] = entry
+        dblock, views = entry
+        pair = views.get(self.B)
+        if pair is None:
+            pair = (dblock[:self.B * self.dx].view(self.B, self.dx),
+                    dblock[self.batch * self.dx:self.batch * self.dx + self.B * self.dy].view(self.B, self.dy))
+            views[self.B] = pair
+        with torch.cuda.device(idx):
+            stream = torch.cuda.current_stream().cuda_stream
+            nbytes = self.block.numel() * 4 if self.B == self.batch else None
+            L = _lib.lib()
+            if nbytes is not None:      # full batch: x and y are adjacent, one copy
+                _lib.check(L.ddpb_memcpy_h2d_async(dblock.data_ptr(), self.block.data_ptr(), nbytes, stream), "h2d")
+            else:
+                _lib.check(L.ddpb_memcpy_h2d_async(pair[0].data_ptr(), self.host[0].data_ptr(), self.B * self.dx * 4, stream), "h2d")
+                _lib.check(L.ddpb_memcpy_h2d_async(pair[1].data_ptr(), self.host[1].data_ptr(), self.B * self.dy * 4, stream), "h2d")
+        self._copied_to = (idx, pair)
+        return pair
+
+
+class DeviceBatch:
+    """Handle of a batch of the HBM-resident dataset: `B` rows selected by an index row."""
+
+    __slots__ = ("x", "y", "idx_ptr", "B", "which", "keep")
+
+    def __init__(self, x, y, idx_ptr, B, which, keep):
+        self.x, self.y, self.idx_ptr, self.B, self.which, self.keep = x, y, idx_ptr, B, which, keep
+
+    def cuda(self, device=None, non_blocking=False):
+        return self
+
+    def to(self, *args, **kwargs):
+        return self
+
+    def size(self, dim=None):
+        width = self.x.shape[1] if self.which == 0 else self.y.shape[1]
+        shape = torch.Size((self.B, width))
+        return shape if dim is None else shape[dim]
+
+    @property
+    def shape(self):
+        return self.size()
+
+
+def _dense(dataset):
+    """Dense [n,dx], [n,dy] float32 CPU tensors of a map-style dataset of (x, y) pairs."""
+    if hasattr(dataset, "x_dense") and hasattr(dataset, "y_dense"):
+        return dataset.x_dense, dataset.y_dense
+    xs, ys = zip(*(dataset[i] for i in range(len(dataset))))
+    x = torch.stack([torch.as_tensor(v, dtype=torch.float32).reshape(-1) for v in xs]).contiguous()
+    y = torch.stack([torch.as_tensor(v, dtype=torch.float32).reshape(-1) for v in ys]).contiguous()
+    return x, y
+
+
+class DataLoader:
+    """DataLoader(dataset, batch_size, shuffle=False, sampler=None, pin_memory, num_workers, drop_last)
+    with the argument meaning of torch's (call sites: demo.py:144-154).
+
+    num_workers is accepted and ignored: batch assembly is one native gather (microseconds),
+    there is nothing for worker processes to do.  shuffle=True without a sampler is not
+    used by the reference and is rejected rather than approximated."""
+
+    STAGES = 4
+    EPOCH_ROWS = 256        # index rows uploaded at a time on the device-resident path
+
+    def __init__(self, dataset, batch_size=1, shuffle=False, sampler=None, pin_memory=False, num_workers=0,
+                 drop_last=False, device_resident=None, **unused):
+        if shuffle and sampler is None:
+            raise NotImplementedError("DataLoader(shuffle=True) without a sampler is not part of the reference path")
+        self.dataset, self.batch_size, self.sampler, self.drop_last = dataset, int(batch_size), sampler, drop_last
+        self.num_workers, self.pin_memory = num_workers, pin_memory
+        self.x, self.y = _dense(dataset)
+        self.dx, self.dy = self.x.shape[1], self.y.shape[1]
+        if device_resident is None:
+            device_resident = os.environ.get("DDPB_DEVICE_DATA", "0") == "1"
+        self.device_resident = bool(device_resident)
+        self._stages = None
+        self._next_stage = 0
+        self._dev = None          # (x_dev, y_dev) on the device-resident path
+        self._rows = None         # (epoch0, host int32 rows, device rows)
+
+    def __len__(self):
+        n = len(self.sampler) if self.sampler is not None else len(self.dataset)
+        return n // self.batch_size if self.drop_last else math.ceil(n / self.batch_size)
+
+    def _indices(self):
+        if self.sampler is None:
+            return np.arange(len(self.dataset), dtype=np.int64)
+        if hasattr(self.sampler, "indices"):
+            return self.sampler.indices()
+        return np.fromiter(iter(self.sampler), dtype=np.int64)
+
+    def __iter__(self):
+        return self._iter_device() if self.device_resident else self._iter_host()
+
+    def _iter_host(self):
+        if self._stages is None:
+            self._stages = [_Stage(self.batch_size, self.dx, self.dy) for _ in range(self.STAGES)]
+        idx = self._indices()
+        L = _lib.lib()
+        xp, yp = self.x.data_ptr(), self.y.data_ptr()
+        for start in range(0, len(idx), self.batch_size):
+            B = min(self.batch_size, len(idx) - start)
+            if B < self.batch_size and self.drop_last:
+                return
+            stage = self._stages[self._next_stage]
+            self._next_stage = (self._next_stage + 1) % self.STAGES
+            stage.set_rows(B)
+            _lib.check(L.ddpb_host_gather(xp, yp, idx.ctypes.data + start * 8, B, self.dx, self.dy,
+                                          stage.host[0].data_ptr(), stage.host[1].data_ptr()), "ddpb_host_gather")
+            yield HostBatch(stage, 0), HostBatch(stage, 1)
+
+    def _iter_device(self):
+        if self._dev is None:
+            self._dev = (self.x.cuda(), self.y.cuda())
+        epoch = self.sampler.epoch if self.sampler is not None else 0
+        per_epoch = len(self.sampler) if self.sampler is not None else len(self.dataset)
+        if self._rows is None or not (self._rows[0] <= epoch < self._rows[0] + self._rows[1].shape[0]):
+            if self.sampler is not None and hasattr(self.sampler, "epochs_i32"):
+                rows = self.sampler.epochs_i32(epoch, self.EPOCH_ROWS)
+            else:
+                rows = np.tile(self._indices().astype(np.int32), (1, 1))
+            self._rows = (epoch, rows, torch.from_numpy(rows).cuda())
+        epoch0, rows, drows = self._rows
+        row = epoch - epoch0 if rows.shape[0] > 1 else 0
+        base = drows.data_ptr() + row * rows.shape[1] * 4
+        for start in range(0, per_epoch, self.batch_size):
+            B = min(self.batch_size, per_epoch - start)
+            if B < self.batch_size and self.drop_last:
+                return
+            ptr = base + start * 4
+            yield (DeviceBatch(self._dev[0], self._dev[1], ptr, B, 0, drows),
+                   DeviceBatch(self._dev[0], self._dev[1], ptr, B, 1, drows))

@@ -1,0 +1,321 @@
+"""DistributedDataParallel with the call shapes of demo.py:70,72 and
+demo_one_model_multi_gpu.py:98.
+
+    model = DistributedDataParallel(ToyModel().cuda(), device_ids=[local_rank])
+    out = model(data); loss = MSELoss()(out, target); loss.backward(); optimizer.step()
+
+What the reference's wrapper does with ~30 tensors, hooks and a C++ Reducer
+(torch:nn/parallel/distributed.py:655-900; reducer.hpp) becomes, for the toy model:
+
+  * construction (collective): parameters are flattened into ONE fp32 HBM vector in
+    module.parameters() order, every nn.Parameter is re-pointed at its slice, `.grad`
+    at the matching slice of ONE flat gradient bucket (gradient_as_bucket_view), shapes are
+    verified across ranks and rank 0's values are broadcast (demo.py:70; torch:...:879-890);
+  * forward/loss/backward/step: described lazily, launched by engine.py as one fused
+    kernel per iteration (single rank) or fused-gradient kernel -> ncclAllReduce of the
+    bucket -> fused average+Adam pass (several ranks).
+
+There is no fallback to PyTorch modules: a model this package has no kernels for, or a
+CPU-resident module, raises.
+"""
+import ctypes
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from . import _lib
+from .data import DeviceBatch, HostBatch
+from .engine import engine_for
+from .toy_model_and_data import ToyModel
+
+_OWNERS = {}          # id(nn.Parameter) -> backend
+LOSS_RING = 1024      # loss slots per model; a LossValue stays readable for this many steps
+
+
+def owner_of(param):
+    try:
+        return _OWNERS[id(param)]
+    except KeyError:
+        raise _lib.DdpB200Error("this parameter does not belong to a distributed_training_pytorch_b200."
+                                "DistributedDataParallel model; wrap the model before building its optimizer") from None
+
+
+class Output:
+    """Lazy result of wrapper(data).  Holds the batch; values exist after `.tensor()`."""
+
+    def __init__(self, backend, data):
+        self.backend, self.data = backend, data
+
+    def tensor(self):
+        return self.backend.forward_now(self.data)
+
+    def detach(self):
+        return self.tensor()
+
+    def cpu(self):
+        return self.tensor().cpu()
+
+
+class DistributedDataParallel:
+    def __init__(self, module, device_ids=None, output_device=None, dim=0, broadcast_buffers=True,
+                 process_group=None, bucket_cap_mb=25, find_unused_parameters=False,
+                 gradient_as_bucket_view=True, static_graph=False, lazy_step=None, **unused):
+        self.module = module
+        self.process_group = process_group
+        self.bucket_cap_mb = bucket_cap_mb
+        self.device_ids = device_ids
+        if isinstance(module, ToyModel) and module.hidden == _lib.TOY_HIDDEN:
+            self._backend = ToyBackend(module, process_group, lazy_step)
+        else:
+            raise NotImplementedError(
+                f"no sm_100a kernels for {type(module).__name__}"
+                f"{'(hidden=%d)' % module.hidden if hasattr(module, 'hidden') else ''}; "
+                "there is no PyTorch fallback in this package")
+        self.require_backward_grad_sync = True
+
+    # -- nn.Module-like surface ---------------------------------------------------
+    def __call__(self, data):
+        return Output(self._backend, data)
+
+    forward = __call__
+
+    def parameters(self, recurse=True):
+        return self.module.parameters(recurse)
+
+    def named_parameters(self, *a, **k):
+        return self.module.named_parameters(*a, **k)
+
+    def state_dict(self, *a, **k):
+        self._backend.engine.flush()
+        return {"module." + key: v for key, v in self.module.state_dict(*a, **k).items()}
+
+    def train(self, mode=True):
+        self.module.train(mode)
+        return self
+
+    def eval(self):
+        return self.train(False)
+
+    def flat_parameters(self):
+        """The flat fp32 parameter vector (after everything described so far has been launched)."""
+        self._backend.engine.flush()
+        return self._backend.params
+
+
+class ToyBackend:
+    """Flat state + job description of one H=10 ToyModel on one device."""
+
+    def __init__(self, module, process_group, lazy_step):
+        tensors = list(module.parameters())
+        dev = tensors[0].device
+        if dev.type != "cuda" or any(p.device != dev for p in tensors):
+            raise _lib.DdpB200Error("DistributedDataParallel needs the module on ONE CUDA device (call .cuda() first, "
+                                    "demo.py:69-70); there is no CPU path")
+        if any(p.dtype != torch.float32 for p in tensors):
+            raise _lib.DdpB200Error("parameters must be float32, like the reference's")
+        self.device = dev
+        self.engine = engine_for(dev.index if dev.index is not None else torch.cuda.current_device())
+        self.num_tensors = len(tensors)
+        P = sum(p.numel() for p in tensors)
+        assert P == _lib.TOY_PARAMS
+        self.P = P
+        with torch.cuda.device(dev):
+            self.params = torch.empty(P, dtype=torch.float32, device=dev)
+            self.grads = torch.zeros(P + 1, dtype=torch.float32, device=dev)   # [P] = sum (o-t)^2 of the batch
+            off = 0
+            for p in tensors:
+                n = p.numel()
+                self.params[off:off + n].copy_(p.data.reshape(-1))
+                p.data = self.params[off:off + n].view(p.shape)
+                p.grad = self.grads[off:off + n].view(p.shape)
+                _OWNERS[id(p)] = self
+                off += n
+            init = np.zeros(4, np.int64)
+            init[2:] = np.array([1.0, 1.0], np.float64).view(np.int64)
+            self.state = torch.from_numpy(init).to(dev)
+            self.loss_ring = torch.zeros(LOSS_RING, dtype=torch.float32, device=dev)
+            self.loss_host = torch.zeros(LOSS_RING, dtype=torch.float32, pin_memory=True)
+            self.m = self.v = None
+        self.world, self.rank, self.backend_name = 1, 0, None
+        self.process_group = process_group
+        if dist.is_available() and dist.is_initialized():
+            self.world, self.rank = dist.get_world_size(process_group), dist.get_rank(process_group)
+            self.backend_name = dist.get_backend(process_group)
+        self._sync_replicas()
+        self.lazy = (self.world == 1) if lazy_step is None else bool(lazy_step) and self.world == 1
+        self.opt_kind, self.hyper = None, None
+        self.seq = 0                    # host mirror of state.seq
+        self.waiting = None             # Loss whose backward() was called and not yet described
+        self.grads_fresh = False        # a GRAD job was described; an optimizer step may consume it
+        self.keep = []                  # tensors referenced by the described job
+        self.job = _lib.ToyJob()
+        j = self.job
+        j.params, j.grads = self.params.data_ptr(), self.grads.data_ptr()
+        j.state, j.loss_ring, j.loss_ring_n = self.state.data_ptr(), self.loss_ring.data_ptr(), LOSS_RING
+        j.idx_rows, j.idx_stride = 1, 0
+        self._out = None
+
+    # -- construction-time collective (demo.py:70,72) --------------------------------
+    def _sync_replicas(self):
+        if self.world == 1:
+            return
+        shapes = [None] * self.world
+        dist.all_gather_object(shapes, int(self.P), group=self.process_group)
+        if any(s != self.P for s in shapes):
+            raise _lib.DdpB200Error(f"parameter counts differ across ranks: {shapes}")
+        if self.backend_name == "nccl":
+            comm = self.engine.ensure_comm(self.process_group)
+            _lib.check(self.engine.lib.ddpb_broadcast_f32(comm, self.params.data_ptr(), self.P, 0, self.engine.stream()),
+                       "ddpb_broadcast_f32")
+        else:                                   # gloo / mpi: stage through the host group
+            host = self.params.cpu()
+            dist.broadcast(host, src=0, group=self.process_group)
+            self.params.copy_(host)
+
+    # -- optimizer binding -----------------------------------------------------------
+    def attach_optimizer(self, kind, hyper):
+        self.opt_kind, self.hyper = kind, hyper
+        with torch.cuda.device(self.device):
+            self.m = torch.zeros(self.P, dtype=torch.float32, device=self.device)
+            self.v = torch.zeros(self.P, dtype=torch.float32, device=self.device)
+        j = self.job
+        j.m, j.v, j.opt = self.m.data_ptr(), self.v.data_ptr(), kind
+        j.lr = hyper["lr"]
+        if kind == _lib.OPT_ADAM:
+            j.beta1, j.beta2 = hyper["betas"]
+            j.eps = hyper["eps"]
+        else:
+            j.beta1 = j.beta2 = 1.0
+            j.momentum = hyper["momentum"]
+
+    def optimizer_state_dict(self):
+        self.engine.flush()
+        return {"step": int(self.state[0].item()), "exp_avg": self.m, "exp_avg_sq": self.v}
+
+    # -- describing work ---------------------------------------------------------------
+    def _bind_batch(self, data, target):
+        j = self.job
+        if isinstance(data, HostBatch):
+            data = data.cuda(self.device)
+        if isinstance(target, HostBatch):
+            target = target.cuda(self.device)
+        if isinstance(data, DeviceBatch):
+            j.x, j.y, j.idx, j.B = data.x.data_ptr(), data.y.data_ptr(), data.idx_ptr, data.B
+            j.idx_stride = data.B
+            self.keep = [data.keep]
+            return
+        if not (isinstance(data, torch.Tensor) and data.is_cuda and data.dtype == torch.float32
+                and data.dim() == 2 and data.shape[1] == 2 and data.is_contiguous()):
+            raise _lib.DdpB200Error("model input must be a contiguous float32 CUDA tensor [B,2] (or a loader batch)")
+        j.x, j.idx, j.B, j.idx_stride = data.data_ptr(), None, data.shape[0], 0
+        self.keep = [data]
+        if target is not None:
+            if isinstance(target, DeviceBatch):
+                raise _lib.DdpB200Error("target is a device-resident batch handle but data is not")
+            if not (isinstance(target, torch.Tensor) and target.is_cuda and target.dtype == torch.float32
+                    and target.numel() == data.shape[0] and target.is_contiguous()):
+                raise _lib.DdpB200Error("target must be a contiguous float32 CUDA tensor [B,1]")
+            j.y = target.data_ptr()
+            self.keep.append(target)
+
+    def _describe(self, loss, mode):
+        self._bind_batch(loss.output.data, loss.target)
+        self.job.mode = mode
+        loss.slot = self.seq % LOSS_RING
+        self.seq += 1
+        self.grads_fresh = mode == _lib.MODE_GRAD
+        self.engine.enqueue(self)
+        if self.world > 1:
+            self.engine.flush()           # start the bucket all-reduce now: it overlaps whatever the host does next
+
+    def after_launch(self, stream):
+        """Called by the engine right after the fused kernel of this model went out."""
+        self.keep = []
+        if self.world > 1 and self.job.mode == _lib.MODE_GRAD and self._sync_grads:
+            self._allreduce_bucket(stream)
+
+    _sync_grads = True
+
+    def _allreduce_bucket(self, stream):
+        n = self.P + 1                    # the loss sum rides in the bucket's last element
+        if self.backend_name == "nccl":
+            _lib.check(self.engine.lib.ddpb_allreduce_sum_f32(self.engine.comm, self.grads.data_ptr(), n, stream),
+                       "ddpb_allreduce_sum_f32")
+        else:
+            host = self.grads.cpu()
+            dist.all_reduce(host, group=self.process_group)
+            self.grads.copy_(host)
+
+    def request_backward(self, loss):
+        if self.waiting is not None and self.waiting is not loss:
+            self._describe(self.waiting, _lib.MODE_GRAD)      # an earlier backward never got its step
+        if self.lazy and self.opt_kind is not None:
+            self.waiting = loss                               # decide GRAD vs STEP when step() or a read arrives
+        else:
+            self.waiting = None
+            self._describe(loss, _lib.MODE_GRAD)
+
+    def discard_pending_backward(self):
+        self.waiting = None
+        self.grads_fresh = False
+
+    def request_step(self):
+        if self.opt_kind is None:
+            raise _lib.DdpB200Error("no optimizer attached")
+        if self.waiting is not None:
+            loss, self.waiting = self.waiting, None
+            self._describe(loss, _lib.MODE_STEP)
+            return
+        if not self.grads_fresh:
+            return                                            # torch skips parameters whose grad is None
+        self.grads_fresh = False
+        self.engine.flush()
+        lib, stream, h = self.engine.lib, self.engine.stream(), self.hyper
+        scale = 1.0 / self.world
+        if self.opt_kind == _lib.OPT_ADAM:
+            _lib.check(lib.ddpb_fused_avg_adam_dev(self.grads.data_ptr(), self.params.data_ptr(), self.m.data_ptr(),
+                                                   self.v.data_ptr(), self.P, scale, h["lr"], h["betas"][0],
+                                                   h["betas"][1], h["eps"], self.state.data_ptr(), 1, stream),
+                       "ddpb_fused_avg_adam_dev")
+            self.engine.launches += 2
+        else:
+            self._sgd_steps = getattr(self, "_sgd_steps", 0) + 1
+            _lib.check(lib.ddpb_fused_avg_sgd(self.grads.data_ptr(), self.params.data_ptr(), self.m.data_ptr(), self.P,
+                                              scale, h["lr"], h["momentum"], self._sgd_steps, stream),
+                       "ddpb_fused_avg_sgd")
+            self.engine.launches += 1
+
+    # -- reading results ----------------------------------------------------------------
+    def _ensure_described(self, loss):
+        if loss.slot is None:
+            if self.waiting is loss:
+                self.waiting = None
+            self._describe(loss, _lib.MODE_GRAD)
+
+    def read_loss(self, loss):
+        """Local mean loss as a 0-dim CPU tensor; blocks like the reference's .cpu() (demo.py:115)."""
+        self._ensure_described(loss)
+        self.engine.flush()
+        lib, stream = self.engine.lib, self.engine.stream()
+        off = 4 * loss.slot
+        _lib.check(lib.ddpb_memcpy_d2h_async(self.loss_host.data_ptr() + off, self.loss_ring.data_ptr() + off, 4, stream),
+                   "ddpb_memcpy_d2h_async")
+        _lib.check(lib.ddpb_stream_sync(stream), "ddpb_stream_sync")
+        return self.loss_host[loss.slot].clone()
+
+    def loss_device_view(self, loss):
+        self._ensure_described(loss)
+        self.engine.flush()
+        return self.loss_ring[loss.slot]
+
+    def forward_now(self, data):
+        """Eager forward (MODE_FWD) for callers that want the output values."""
+        self.engine.flush()
+        self._bind_batch(data, None)
+        B = self.job.B
+        out = torch.empty(B, 1, dtype=torch.float32, device=self.device)
+        self.job.out, self.job.mode = out.data_ptr(), _lib.MODE_FWD
+        self.engine.enqueue(self)
+        self.engine.flush()
+        return out

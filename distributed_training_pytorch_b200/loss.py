@@ -1,0 +1,78 @@
+"""nn.MSELoss() with the call shape of demo.py:86,106-118: loss(out, target) returns an
+object with .backward() and .detach().cpu().  Nothing is computed when it is built; the
+mean-squared error comes out of the same fused kernel that produces the gradients."""
+import torch
+
+from . import _lib
+
+
+class MSELoss:
+    def __init__(self, reduction="mean"):
+        if reduction != "mean":
+            raise NotImplementedError("only reduction='mean' (the reference's nn.MSELoss()) is implemented")
+
+    def __call__(self, output, target):
+        from .ddp import Output
+        if not isinstance(output, Output):
+            raise TypeError("MSELoss expects the output of a distributed_training_pytorch_b200.DistributedDataParallel "
+                            "forward; eager tensors are not supported (no PyTorch fallback)")
+        return Loss(output, target)
+
+
+class Loss:
+    """A scalar that exists on the device once its step has been launched."""
+
+    def __init__(self, output, target):
+        self.output, self.target = output, target
+        self.backend = output.backend
+        self.slot = None           # (flat model, ring slot) once described to the engine
+        self.backward_called = False
+
+    # -- autograd-like surface ----------------------------------------------
+    def backward(self):
+        self.backward_called = True
+        self.backend.request_backward(self)
+
+    def detach(self):
+        return LossValue(self)
+
+    def item(self):
+        return float(self.detach().cpu())
+
+    def __float__(self):
+        return self.item()
+
+    def cpu(self):
+        return self.detach().cpu()
+
+
+class LossValue:
+    """Result of loss.detach(): still lazy; .cpu() is the synchronisation point
+    (demo.py:115,117), exactly where the reference blocks on its D2H copy."""
+
+    def __init__(self, loss):
+        self._loss = loss
+
+    def cpu(self):
+        return self._loss.backend.read_loss(self._loss)
+
+    def item(self):
+        return float(self.cpu())
+
+    def __float__(self):
+        return self.item()
+
+    def cuda(self, *a, **k):
+        return self.device_tensor()
+
+    def device_tensor(self):
+        """0-dim CUDA tensor view of the loss slot (valid until the ring wraps)."""
+        return self._loss.backend.loss_device_view(self._loss)
+
+    # wandb.log({'loss/loss': loss.detach()}) (demo_one_model_multi_gpu.py:130) stringifies / converts
+    def __repr__(self):
+        return f"LossValue({self.item():.6g})"
+
+    def __array__(self, dtype=None, copy=None):
+        import numpy as np
+        return np.asarray(self.item(), dtype=dtype or np.float32)

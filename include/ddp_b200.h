@@ -1,0 +1,145 @@
+/*
+ * ddp_b200.h -- C ABI of libddp_b200.so: the B200 (sm_100a) implementation of the
+ * data-parallel training step of ammunk/distributed-training-pytorch's toy model.
+ *
+ * Conventions
+ *   - every entry point returns 0 on success; non-zero = failure, text in
+ *     ddpb_last_error() (thread-local).  CUDA failures return 1000+cudaError_t,
+ *     NCCL failures 2000+ncclResult_t, argument errors 1..99.
+ *   - the caller (PyTorch) owns every tensor buffer: pointers are raw device (or,
+ *     where stated, host) addresses, sizes are element counts, streams are
+ *     cudaStream_t passed as void*.  The library owns only the opaque handles it
+ *     creates (NCCL communicator, peer workspaces, TMA descriptors).
+ *   - fp32 storage everywhere, exactly like the reference's models.
+ *
+ * The reference has no FFI of its own (it is 6 Python files that call PyTorch);
+ * each declaration cites the reference line whose work it replaces.  Paths
+ * without a prefix are relative to the reference repository root; "torch:" paths
+ * are relative to site-packages/torch 2.11.0.
+ */
+#ifndef DDP_B200_H
+#define DDP_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DDPB_VERSION 100           /* 0.1.0 */
+#define DDPB_TOY_HIDDEN 10         /* toy_model_and_data.py:13-21 */
+#define DDPB_TOY_PARAMS 371        /* 3H^2 + 7H + 1 */
+#define DDPB_MAX_JOBS 4            /* models per ddpb_toy_step launch */
+
+/* ---- introspection ------------------------------------------------------- */
+int ddpb_version(void);
+const char *ddpb_last_error(void);
+/* device properties the host layer sizes its grids with (148 SMs on B200). */
+int ddpb_device_info(int device, int *cc_major, int *cc_minor, int *sm_count);
+
+/* ---- sampler: DistributedSampler(dataset, shuffle=True) ------------------- */
+/* demo.py:144 builds it, demo.py:96-98 reseeds it per epoch.  Host code, bit-exact
+ * restatement of torch.randperm on the CPU generator (mt19937, forward
+ * Fisher-Yates) and of torch:utils/data/distributed.py:84-141. */
+int ddpb_randperm(uint64_t seed, int64_t n, int64_t *out /* host [n] */);
+/* returns the number of indices written (ceil(n/world) without drop_last) or -1 */
+int64_t ddpb_sampler_indices(int64_t n, int world, int rank, int shuffle, uint64_t seed,
+                             uint64_t epoch, int drop_last, int64_t *out /* host */, int64_t cap);
+/* The same stream for epochs [epoch0, epoch0+nepochs) as int32 rows of `stride`
+ * entries (row e holds the indices of epoch0+e), ready to be uploaded once for the
+ * device-resident data path. */
+int ddpb_sampler_epochs_i32(int64_t n, int world, int rank, int shuffle, uint64_t seed,
+                            uint64_t epoch0, int nepochs, int drop_last,
+                            int32_t *out /* host [nepochs*stride] */, int64_t stride);
+
+/* ---- batch assembly ------------------------------------------------------- */
+/* Host: replaces ToyData.__getitem__ x B + default_collate (toy_model_and_data.py:32-33,
+ * demo.py:99) by one gather from the dense dataset into (pinned) staging rows. */
+int ddpb_host_gather(const float *X, const float *Y, const int64_t *idx, int64_t B, int dx, int dy,
+                     float *outX, float *outY);
+/* Device: dataset resident in HBM, batch = rows idx[0..B) (replaces the per-step
+ * H2D copies of demo.py:102-103). */
+int ddpb_gather_batch(const float *X, const float *Y, const int32_t *idx, int64_t B, int dx, int dy,
+                      float *outX, float *outY, void *stream);
+
+/* ---- the fused toy-model step (H = 10) ------------------------------------ */
+/* One launch runs, for up to DDPB_MAX_JOBS independent models, what demo.py:104-111
+ * spends ~70 library kernels on: ToyModel.forward (toy_model_and_data.py:24-25),
+ * nn.MSELoss (demo.py:106,108), loss.backward() (demo.py:107,109) and, in STEP mode,
+ * optim.Adam.step (demo.py:110-111) -- one 8-CTA thread-block cluster per model,
+ * gradients reduced through distributed shared memory. */
+enum {
+    DDPB_MODE_FWD = 0,    /* out[B,1] = model(x) */
+    DDPB_MODE_GRAD = 1,   /* grads[P] = d(mean loss)/dparams (local batch), grads[P] = sum (o-t)^2 */
+    DDPB_MODE_STEP = 2    /* GRAD + in-place Adam/SGD update of params (single-rank fused path) */
+};
+enum { DDPB_OPT_ADAM = 0, DDPB_OPT_SGD = 1 };
+
+/* Device-resident optimizer counters (32 bytes, zero-initialised by the host layer).
+ * Kept on the device so a captured CUDA graph can replay steps without new arguments. */
+typedef struct ddpb_opt_state {
+    long long step;    /* optimizer steps applied so far */
+    long long seq;     /* gradient evaluations so far (selects loss slot / index row) */
+    double beta1_pow;  /* beta1^step (1.0 at step 0) */
+    double beta2_pow;  /* beta2^step */
+} ddpb_opt_state;
+
+typedef struct ddpb_toy_job {
+    float *params;            /* [371] flat, module.parameters() order: W0,b0,...,W4,b4 */
+    float *grads;             /* [372] flat gradient bucket; element 371 carries sum (o-t)^2 */
+    float *m, *v;             /* Adam moments [371] (m = SGD momentum buffer); STEP only */
+    ddpb_opt_state *state;    /* device counters */
+    float *loss_ring;         /* [loss_ring_n] mean-loss slots, slot = seq % loss_ring_n */
+    const float *x;           /* [B,2] batch, or the whole dataset when idx != NULL */
+    const float *y;           /* [B,1] targets, or the whole dataset */
+    const int32_t *idx;       /* NULL, or [idx_rows][idx_stride] sample indices; row = seq % idx_rows */
+    float *out;               /* FWD: [B,1] */
+    int32_t B;                /* local batch (1..65536) */
+    int32_t mode;             /* DDPB_MODE_* */
+    int32_t opt;              /* DDPB_OPT_* */
+    int32_t loss_ring_n;
+    int32_t idx_rows, idx_stride;
+    double lr, beta1, beta2, eps, momentum;
+} ddpb_toy_job;
+
+int ddpb_toy_step(const ddpb_toy_job *jobs /* host */, int njobs, void *stream);
+
+/* ---- optimizer over a flat bucket ----------------------------------------- */
+/* One pass over a (reduced) gradient bucket: g = bucket * grad_scale (the 1/W of
+ * DDP's averaging, torch:distributed/algorithms/ddp_comm_hooks/default_hooks.py:24-29),
+ * then torch's Adam op order (torch:optim/adam.py:457-547; demo.py:80-81,110-111).
+ * 28 B/param of HBM traffic.  `step` is the 1-based step being applied; the bias
+ * corrections are computed by the host in double, as torch does. */
+int ddpb_fused_avg_adam(const float *bucket, float *p, float *m, float *v, int64_t n,
+                        float grad_scale, double lr, double beta1, double beta2, double eps,
+                        int64_t step, void *stream);
+/* Same with device-resident counters (graph-replayable); advances state->step. */
+int ddpb_fused_avg_adam_dev(const float *bucket, float *p, float *m, float *v, int64_t n,
+                            float grad_scale, double lr, double beta1, double beta2, double eps,
+                            ddpb_opt_state *state, int advance, void *stream);
+/* SGD with optional momentum (north_star lists it beside Adam; torch:optim/sgd.py). */
+int ddpb_fused_avg_sgd(const float *bucket, float *p, float *buf, int64_t n, float grad_scale,
+                       double lr, double momentum, int64_t step, void *stream);
+
+
+
+/* ---- communicator: NCCL over NVLink --------------------------------------- */
+/* Replaces the c10d Reducer's ncclAllReduce per bucket (demo.py:107,109 via
+ * torch:include/torch/csrc/distributed/c10d/reducer.hpp) and DDP's construction-time
+ * parameter broadcast (demo.py:70,72; torch:nn/parallel/distributed.py:879-890). */
+int ddpb_nccl_load(const char *path_or_null);           /* dlopen the NCCL torch already loaded */
+int ddpb_get_unique_id(char out[128]);                  /* rank 0, then shared through the c10d store */
+int ddpb_comm_create(const char id[128], int rank, int world, int device, void **comm_out);
+int ddpb_comm_destroy(void *comm);
+int ddpb_broadcast_f32(void *comm, float *buf, int64_t n, int root, void *stream);
+int ddpb_allreduce_sum_f32(void *comm, float *buf, int64_t n, void *stream);
+
+/* ---- streams / events helpers the host layer needs without torch calls ----- */
+int ddpb_stream_sync(void *stream);
+int ddpb_memcpy_h2d_async(void *dst_dev, const void *src_host, int64_t bytes, void *stream);
+int ddpb_memcpy_d2h_async(void *dst_host, const void *src_dev, int64_t bytes, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DDP_B200_H */

@@ -13,7 +13,7 @@ small shim that
   * records what wandb.log receives (demo.py:120-121) and the final parameters.
 
 Usage:  python tests/golden/make_golden.py            # spawns torchrun for W=1,2,4,8
-Outputs: ref_w{W}.npz (loss curves, initial + final parameters), dataset.npz,
+Outputs: ref_w{W}.npz (loss curves, initial / step-200 / final parameters), dataset.npz,
          sampler.npz, meta.json.
 """
 import hashlib
@@ -27,6 +27,7 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 REF = "/root/reference"
 SEED = 1234
+MID = 200     # parameters are also snapshotted after this many steps (tight pin before chaos sets in)
 
 
 def _flat(model):
@@ -62,6 +63,9 @@ def worker():
     def _log(d, **k):
         for key, v in d.items():
             logged[key].append(float(v))
+        # both optimizers have stepped when lossY is logged (demo.py:110-121): snapshot after MID steps
+        if len(logged["loss/lossY"]) == MID and "mid_X" not in captured and "models" in captured:
+            captured["mid_X"], captured["mid_Y"] = (_flat(m.module) for m in captured["models"])
 
     wandb.log = _log
     captured = {}
@@ -70,6 +74,7 @@ def worker():
     def setup(config):
         mx, my, ws = stock_setup(config)
         captured["init_X"], captured["init_Y"] = _flat(mx.module), _flat(my.module)
+        captured["models"] = (mx, my)
         return mx, my, ws
 
     def loader(config, dataset):
@@ -85,6 +90,7 @@ def worker():
     torch.manual_seed(SEED)
     sys.argv = [sys.argv[0], "--backend=gloo", "--torchrun", "--dry_run"]
     demo.main()
+    captured.pop("models")
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     np.savez(os.path.join(os.environ["GOLDEN_TMP"], f"w{world}_r{rank}.npz"),
              lossX=np.asarray(logged["loss/lossX"], np.float64),
@@ -113,7 +119,8 @@ def driver():
             assert np.array_equal(r["final_X"], r0["final_X"]) and np.array_equal(r["final_Y"], r0["final_Y"])
         np.savez(os.path.join(HERE, f"ref_w{world}.npz"),
                  lossX=r0["lossX"].astype(np.float32), lossY=r0["lossY"].astype(np.float32),
-                 init_X=r0["init_X"], init_Y=r0["init_Y"], final_X=r0["final_X"], final_Y=r0["final_Y"])
+                 init_X=r0["init_X"], init_Y=r0["init_Y"], final_X=r0["final_X"], final_Y=r0["final_Y"],
+                 mid_X=r0["mid_X"], mid_Y=r0["mid_Y"], mid_step=np.int64(MID))
         meta["runs"][f"w{world}"] = {"final_X_sha": sha(r0["final_X"]), "final_Y_sha": sha(r0["final_Y"]),
                                      "loss0": [float(r0["lossX"][0]), float(r0["lossY"][0])],
                                      "loss999": [float(r0["lossX"][-1]), float(r0["lossY"][-1])]}
