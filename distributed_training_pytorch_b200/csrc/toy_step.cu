@@ -232,7 +232,8 @@ toy_step_kernel(const __grid_constant__ JobList jl) {
             if (valid) {
                 const long long s = idx_row ? (long long)idx_row[b] : (long long)b;
                 const float2 xv = *reinterpret_cast<const float2 *>(job.x + 2 * s);
-                x0 = xv.x; x1 = xv.y; y = job.y[s];
+                x0 = xv.x; x1 = xv.y;
+                if (mode != DDPB_MODE_FWD) y = job.y[s];
             }
             // ---- forward, one sample per lane
             float a0[H], a1[H], a2[H], a3[H];
