@@ -22,16 +22,15 @@ class DdpB200Error(RuntimeError):
 
 
 class OptState(ctypes.Structure):
-    _fields_ = [("step", ctypes.c_longlong), ("seq", ctypes.c_longlong),
-                ("beta1_pow", c_double), ("beta2_pow", c_double)]
+    _fields_ = [("step", ctypes.c_longlong), ("seq", ctypes.c_longlong), ("reserved", ctypes.c_longlong * 2)]
 
 
 class ToyJob(ctypes.Structure):
     _fields_ = [("params", c_void_p), ("grads", c_void_p), ("m", c_void_p), ("v", c_void_p),
-                ("state", c_void_p), ("loss_ring", c_void_p), ("x", c_void_p), ("y", c_void_p),
+                ("state", c_void_p), ("bias_table", c_void_p), ("loss_ring", c_void_p), ("x", c_void_p), ("y", c_void_p),
                 ("idx", c_void_p), ("out", c_void_p),
                 ("B", c_int32), ("mode", c_int32), ("opt", c_int32), ("loss_ring_n", c_int32),
-                ("idx_rows", c_int32), ("idx_stride", c_int32),
+                ("idx_rows", c_int32), ("idx_stride", c_int32), ("bias_table_n", c_int32), ("reserved", c_int32),
                 ("lr", c_double), ("beta1", c_double), ("beta2", c_double), ("eps", c_double),
                 ("momentum", c_double)]
 
@@ -49,7 +48,7 @@ _SIGNATURES = {
     "ddpb_fused_avg_adam": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_float,
                                     c_double, c_double, c_double, c_double, c_int64, c_void_p]),
     "ddpb_fused_avg_adam_dev": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_float,
-                                        c_double, c_double, c_double, c_double, c_void_p, c_int, c_void_p]),
+                                        c_double, c_double, c_double, c_void_p, c_int, c_void_p, c_int, c_void_p]),
     "ddpb_fused_avg_sgd": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_float, c_double, c_double, c_int64, c_void_p]),
     "ddpb_nccl_load": (c_int, [c_char_p]),
     "ddpb_get_unique_id": (c_int, [c_void_p]),
@@ -90,3 +89,22 @@ def check(rc, what=""):
     if rc != 0:
         msg = lib().ddpb_last_error().decode(errors="replace")
         raise DdpB200Error(f"{what or 'libddp_b200'} failed (code {rc}): {msg}")
+
+
+def adam_bias_table(lr, beta1, beta2, max_steps=1 << 22):
+    """[n,2] float32 rows {-(lr/(1-beta1^t)), sqrt(1-beta2^t)} for t = 1..n, computed with
+    Python doubles exactly like torch:optim/adam.py:531-536, n = first step at which both
+    corrections have converged to 1.0 (later steps reuse the last row)."""
+    import numpy as np
+    rows = []
+    t = 0
+    while True:
+        t += 1
+        bc1 = 1 - beta1 ** t
+        bc2 = 1 - beta2 ** t
+        rows.append((-(lr / bc1), bc2 ** 0.5))
+        if bc1 == 1.0 and bc2 == 1.0:
+            break
+        if t >= max_steps:
+            raise DdpB200Error(f"Adam bias corrections for betas=({beta1},{beta2}) do not converge within {max_steps} steps")
+    return np.asarray(rows, dtype=np.float64).astype(np.float32)

@@ -43,17 +43,23 @@ __device__ __forceinline__ AdamScalars make_scalars(double lr, double beta1, dou
     return k;
 }
 
-// b1pow/b2pow are beta^step for the step being applied.  If `state` is given they are
-// derived from the device counters instead (graph replay).
+// b1pow/b2pow are beta^step for the step being applied (host doubles).  If `state` is given the
+// bias-correction scalars come from the host-built table indexed by the device step counter
+// instead (graph replay).
 __global__ void __launch_bounds__(256)
 avg_adam_kernel(const float *__restrict__ bucket, float *__restrict__ p, float *__restrict__ m,
                 float *__restrict__ v, long long n, float grad_scale, double lr, double beta1, double beta2,
-                double eps, double b1pow, double b2pow, const ddpb_opt_state *state) {
+                double eps, double b1pow, double b2pow, const ddpb_opt_state *state,
+                const float2 *__restrict__ bias_table, int bias_table_n) {
+    AdamScalars k;
     if (state) {
-        b1pow = state->beta1_pow * beta1;
-        b2pow = state->beta2_pow * beta2;
+        const long long step = state->step;
+        const float2 bias = bias_table[step < bias_table_n ? step : bias_table_n - 1];
+        k.w1 = (float)(1.0 - beta1); k.b2 = (float)beta2; k.w2 = (float)(1.0 - beta2);
+        k.bc2_sqrt = bias.y; k.eps = (float)eps; k.neg_step = bias.x; k.grad_scale = grad_scale;
+    } else {
+        k = make_scalars(lr, beta1, beta2, eps, b1pow, b2pow, grad_scale);
     }
-    const AdamScalars k = make_scalars(lr, beta1, beta2, eps, b1pow, b2pow, grad_scale);
     const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     const long long nthreads = (long long)gridDim.x * blockDim.x;
     const bool aligned = ((((uintptr_t)bucket) | ((uintptr_t)p) | ((uintptr_t)m) | ((uintptr_t)v)) & 15u) == 0;
@@ -84,11 +90,7 @@ avg_adam_kernel(const float *__restrict__ bucket, float *__restrict__ p, float *
 
 // The counters are advanced by a separate single-thread kernel enqueued right after the
 // update: same stream, so it is ordered after every block of the pass above.
-__global__ void advance_state_kernel(ddpb_opt_state *state, double beta1, double beta2) {
-    state->step += 1;
-    state->beta1_pow *= beta1;
-    state->beta2_pow *= beta2;
-}
+__global__ void advance_state_kernel(ddpb_opt_state *state) { state->step += 1; }
 
 __global__ void __launch_bounds__(256)
 avg_sgd_kernel(const float *__restrict__ bucket, float *__restrict__ p, float *__restrict__ buf, long long n,
@@ -123,19 +125,21 @@ DDPB_API int ddpb_fused_avg_adam(const float *bucket, float *p, float *m, float 
     if (n == 0) return 0;
     avg_adam_kernel<<<stream_grid(n, 4), 256, 0, (cudaStream_t)stream>>>(
         bucket, p, m, v, n, grad_scale, lr, beta1, beta2, eps, std::pow(beta1, (double)step),
-        std::pow(beta2, (double)step), nullptr);
+        std::pow(beta2, (double)step), nullptr, nullptr, 0);
     DDPB_CUDA(cudaGetLastError());
     return 0;
 }
 
 DDPB_API int ddpb_fused_avg_adam_dev(const float *bucket, float *p, float *m, float *v, int64_t n, float grad_scale,
-                                     double lr, double beta1, double beta2, double eps, ddpb_opt_state *state,
-                                     int advance, void *stream) {
-    DDPB_REQUIRE(bucket && p && m && v && n >= 0 && state, "ddpb_fused_avg_adam_dev: bad arguments");
+                                     double beta1, double beta2, double eps, const float *bias_table,
+                                     int bias_table_n, ddpb_opt_state *state, int advance, void *stream) {
+    DDPB_REQUIRE(bucket && p && m && v && n >= 0 && state && bias_table && bias_table_n >= 1,
+                 "ddpb_fused_avg_adam_dev: bad arguments");
     if (n > 0)
         avg_adam_kernel<<<stream_grid(n, 4), 256, 0, (cudaStream_t)stream>>>(
-            bucket, p, m, v, n, grad_scale, lr, beta1, beta2, eps, 0.0, 0.0, state);
-    if (advance) advance_state_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(state, beta1, beta2);
+            bucket, p, m, v, n, grad_scale, 0.0, beta1, beta2, eps, 0.0, 0.0, state,
+            reinterpret_cast<const float2 *>(bias_table), bias_table_n);
+    if (advance) advance_state_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(state);
     DDPB_CUDA(cudaGetLastError());
     return 0;
 }

@@ -6,24 +6,27 @@
 //   loss.backward()        autograd + DDP reducer hooks, demo.py:107       (~45)
 //   optimizer.step()       optim.Adam foreach path, demo.py:110            (~10)
 // Here it is ONE launch for all models of the process: a thread-block cluster of 8 CTAs
-// per model (blockIdx.y = model).  At this size (1 MFLOP, 10 KB) nothing but latency
-// matters, so the design minimises the dependent-instruction chain:
+// per model (blockIdx.y = model).  At this size (1 MFLOP, 10 KB) only latency matters:
+// ncu of the first version (profiles/r01_v0_*) showed one warp per scheduler crawling
+// through a 1900-instruction dependent chain (IPC 0.14).  This version shortens the chain:
 //
-//   * CTA c owns samples [32c, 32c+32) of the batch, one sample per lane.  Its four warps
-//     run the same per-sample forward/backward chain redundantly (one warp per SM
-//     sub-partition, so redundancy costs no time) and each writes a quarter of the
-//     per-sample table (activations + pre-activation gradients, [84 rows][32 samples]).
-//   * The weight gradient dW = dZ^T A is then a [371 x 32] x [32] contraction per CTA:
-//     thread t computes parameters t, t+128, t+256 with conflict-free LDS.128 rows.
-//   * The eight per-CTA partials meet through distributed shared memory: CTA c sums
-//     slice [47c, 47c+47) over the cluster in a fixed order (deterministic), and - in
-//     STEP mode - applies Adam/SGD to that slice with operands prefetched at kernel
-//     start.  Element 371 of the slice table carries sum (o-t)^2, i.e. the loss.
+//   * CTA c owns samples [32c, 32c+32) of the batch, one sample per lane.  Its four compute
+//     warps split each layer's OUTPUT neurons (warp w owns neurons w, w+4, w+8): a layer is
+//     <= 30 FMAs per warp, the activations meet in a shared-memory table
+//     ([84 rows][32 samples]: inputs, activations, pre-activation gradients), one named
+//     barrier per layer.  The same table is the operand of the weight-gradient contraction
+//     dW = dZ^T A ([371 x 32] x [32] per CTA), thread t computing parameters t, t+128, t+256
+//     with conflict-free LDS.128 rows and four independent partial sums.
+//   * Two more warps per CTA are the optimizer: they prefetch p, m, v and the bias-correction
+//     scalars of their 47-parameter slice at kernel start, sleep on the cluster barrier, then
+//     sum the eight per-CTA partials through distributed shared memory in a fixed order
+//     (deterministic) and apply Adam/SGD.  Element 371 of the slice table carries
+//     sum (o-t)^2, i.e. the loss.
 //
 // Arithmetic order of the per-sample chain (fmaf from the bias, k ascending) and of the
 // optimizer (torch's op order, explicit round-to-nearest intrinsics, no contraction) is
-// the one oracle/ddp_oracle.c uses, so forward values and the update are bit-identical
-// given identical gradients; only the batch-sum order differs.
+// the one oracle/ddp_oracle.c uses: forward values are bit-identical, and so is the update
+// given identical gradients; only the batch-sum order of the gradients differs.
 #include "common.cuh"
 #include <cooperative_groups.h>
 #include <cstddef>
@@ -35,15 +38,17 @@ namespace {
 constexpr int H = DDPB_TOY_HIDDEN;
 constexpr int P = DDPB_TOY_PARAMS;
 constexpr int kCluster = 8;
-constexpr int kThreads = 128;
+constexpr int kComputeThreads = 128;             // 4 warps: the per-sample chain and the weight gradients
+constexpr int kThreads = 192;                    // + 2 optimizer warps
 constexpr int kLanes = 32;                       // samples per CTA and pass
 constexpr int kChunk = kCluster * kLanes;        // samples per cluster pass
 constexpr int kWRow = 12;                        // padded weight row, 3 x float4
 constexpr int kRowStride = 36;                   // floats per table row: 144 B keeps LDS.128 conflict-free
+constexpr int kOwned = 3;                        // neurons per warp and layer (ceil(10/4))
 constexpr float kSlope = 0.01f;                  // nn.LeakyReLU() default
 
 // offsets inside the flat parameter vector (module.parameters() order)
-constexpr int OW0 = 0, OB0 = 2 * H;
+constexpr int OB0 = 2 * H;
 constexpr int OW1 = OB0 + H;
 constexpr int kHidden = H * H + H;               // one hidden layer: W then b
 constexpr int OW4 = OW1 + 3 * kHidden, OB4 = OW4 + H;
@@ -56,6 +61,7 @@ constexpr int R_ONE = R_ACT + 4 * H;             // ones (bias gradients)
 constexpr int R_DZ = R_ONE + 1;                  // dz_0 .. dz_3 (H rows each), then dz_4
 constexpr int kRows = R_DZ + 4 * H + 1;
 constexpr int kSlice = (P + 1 + kCluster - 1) / kCluster;   // 47 values per CTA (371 grads + loss sum)
+static_assert(kSlice <= kThreads - kComputeThreads, "the optimizer warps must cover a slice");
 
 struct JobList {
     ddpb_toy_job jobs[DDPB_MAX_JOBS];
@@ -63,7 +69,8 @@ struct JobList {
 
 struct __align__(16) Smem {
     float w0[H][4];            // layer 0: [j][k<2]
-    float wh[3][H][kWRow];     // layers 1..3
+    float wh[3][H][kWRow];     // layers 1..3, [j][k]   (forward: row j)
+    float wt[3][H][kWRow];     // layers 1..3, [k][j]   (backward: column k as a row)
     float w4[kWRow];           // layer 4
     float b[4][kWRow];         // biases of layers 0..3
     float b4[4];
@@ -73,39 +80,13 @@ struct __align__(16) Smem {
 
 __device__ __forceinline__ float lrelu(float z) { return z > 0.f ? z : z * kSlope; }
 
-// Store per-sample values; the four redundant warps split the rows between them.  The
-// split is resolved at compile time inside a warp-uniform switch: selecting rows with a
-// run-time predicate makes nvcc index the register arrays dynamically (local memory).
-template <int ROW, int W>
-__device__ __forceinline__ void put_part(Smem &S, int lane, float val) {
-    if ((ROW & 3) == W) S.table[ROW][lane] = val;
-}
+__device__ __forceinline__ void compute_barrier() { asm volatile("bar.sync 1, %0;" ::"n"(kComputeThreads) : "memory"); }
 
-template <int ROW>
-__device__ __forceinline__ void put(Smem &S, int warp, int lane, float val) {
-    switch (warp) {
-        case 0: put_part<ROW, 0>(S, lane, val); break;
-        case 1: put_part<ROW, 1>(S, lane, val); break;
-        case 2: put_part<ROW, 2>(S, lane, val); break;
-        default: put_part<ROW, 3>(S, lane, val); break;
-    }
-}
-
-template <int ROW0, int W>
-__device__ __forceinline__ void put_vec_part(Smem &S, int lane, const float (&val)[H]) {
-#pragma unroll
-    for (int j = 0; j < H; ++j)
-        if (((ROW0 + j) & 3) == W) S.table[ROW0 + j][lane] = val[j];
-}
-
-template <int ROW0>
-__device__ __forceinline__ void put_vec(Smem &S, int warp, int lane, const float (&val)[H]) {
-    switch (warp) {
-        case 0: put_vec_part<ROW0, 0>(S, lane, val); break;
-        case 1: put_vec_part<ROW0, 1>(S, lane, val); break;
-        case 2: put_vec_part<ROW0, 2>(S, lane, val); break;
-        default: put_vec_part<ROW0, 3>(S, lane, val); break;
-    }
+// Second cluster-barrier phase: pure execution ordering (keeps every CTA's shared memory
+// alive until all remote reads are done), so no release/acquire fence is paid for.
+__device__ __forceinline__ void cluster_rendezvous_relaxed() {
+    asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.aligned;" ::: "memory");
 }
 
 __device__ __forceinline__ void load_row(const float *row, float (&w)[kWRow]) {
@@ -116,34 +97,10 @@ __device__ __forceinline__ void load_row(const float *row, float (&w)[kWRow]) {
     w[8] = c.x; w[9] = c.y; w[10] = c.z; w[11] = c.w;
 }
 
-// Hidden layer forward: nxt = lrelu(W cur + b); mask bit j = (pre-activation j > 0).
-__device__ __forceinline__ void hidden_fwd(const Smem &S, int l, const float (&cur)[H], float (&nxt)[H], unsigned &mask) {
-    mask = 0;
+// Read H consecutive table rows of this lane's sample.
+__device__ __forceinline__ void read_rows(const Smem &S, int row0, int lane, float (&v)[H]) {
 #pragma unroll
-    for (int j = 0; j < H; ++j) {
-        float w[kWRow];
-        load_row(S.wh[l][j], w);
-        float acc = S.b[l + 1][j];
-#pragma unroll
-        for (int k = 0; k < H; ++k) acc = fmaf(w[k], cur[k], acc);
-        mask |= (acc > 0.f ? 1u : 0u) << j;
-        nxt[j] = lrelu(acc);
-    }
-}
-
-// Hidden layer backward: dprev = leaky'(mask_prev) * (W^T dz).
-__device__ __forceinline__ void hidden_bwd(const Smem &S, int l, const float (&dz)[H], unsigned mask_prev, float (&dprev)[H]) {
-#pragma unroll
-    for (int k = 0; k < H; ++k) dprev[k] = 0.f;
-#pragma unroll
-    for (int j = 0; j < H; ++j) {
-        float w[kWRow];
-        load_row(S.wh[l][j], w);
-#pragma unroll
-        for (int k = 0; k < H; ++k) dprev[k] = fmaf(dz[j], w[k], dprev[k]);
-    }
-#pragma unroll
-    for (int k = 0; k < H; ++k) dprev[k] = ((mask_prev >> k) & 1u) ? dprev[k] : dprev[k] * kSlope;
+    for (int k = 0; k < H; ++k) v[k] = S.table[row0 + k][lane];
 }
 
 // Which table rows produce the gradient of flat parameter i:  grad_i = sum_b dz_row[b] * a_row[b].
@@ -161,6 +118,21 @@ __device__ __forceinline__ void rows_of_param(int i, int &row_dz, int &row_a) {
     }
 }
 
+__device__ __forceinline__ void stage_weights(Smem &S, const float *__restrict__ prm, int tid) {
+    for (int i = tid; i < P; i += kThreads) {
+        const float val = prm[i];
+        if (i < OB0) S.w0[i / 2][i & 1] = val;
+        else if (i < OW1) S.b[0][i - OB0] = val;
+        else if (i < OW4) {
+            int q = i - OW1, l = q / kHidden, r = q - l * kHidden;
+            if (r < H * H) { S.wh[l][r / H][r % H] = val; S.wt[l][r % H][r / H] = val; }
+            else S.b[l + 1][r - H * H] = val;
+        } else if (i < OB4) S.w4[i - OW4] = val;
+        else S.b4[0] = val;
+    }
+    if (tid < kRowStride) S.table[R_ONE][tid] = 1.f;
+}
+
 __global__ void __cluster_dims__(kCluster, 1, 1) __launch_bounds__(kThreads, 1)
 toy_step_kernel(const __grid_constant__ JobList jl) {
     __shared__ Smem S;
@@ -169,220 +141,228 @@ toy_step_kernel(const __grid_constant__ JobList jl) {
     const int cta = (int)cluster.block_rank();
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int B = job.B, mode = job.mode;
-
-    // ---- 0. early loads: counters, and the optimizer operands of the slice this thread owns
+    const bool compute = tid < kComputeThreads;
     const long long seq = job.state ? job.state->seq : 0;
-    const int own = cta * kSlice + tid;                 // index into the 372-entry slice table
-    const bool owner = tid < kSlice && own <= P;
+
+    // ---- optimizer warps: everything they need from HBM is requested before anything else
+    const int own = cta * kSlice + (tid - kComputeThreads);     // index into the 372-entry slice table
+    const bool owner = !compute && (tid - kComputeThreads) < kSlice && own <= P;
     float p_old = 0.f, m_old = 0.f, v_old = 0.f;
+    float2 bias = make_float2(0.f, 1.f);
     long long step = 0;
-    double b1pow = 1.0, b2pow = 1.0;
-    if (mode == DDPB_MODE_STEP) {
-        step = job.state->step; b1pow = job.state->beta1_pow; b2pow = job.state->beta2_pow;
+    if (mode == DDPB_MODE_STEP && !compute) {
+        step = job.state->step;
         if (owner && own < P) {
             p_old = job.params[own];
             m_old = job.m[own];
-            if (job.opt == DDPB_OPT_ADAM) v_old = job.v[own];
+            if (job.opt == DDPB_OPT_ADAM) {
+                v_old = job.v[own];
+                const long long row = step < job.bias_table_n ? step : job.bias_table_n - 1;
+                bias = reinterpret_cast<const float2 *>(job.bias_table)[row];
+            }
         }
     }
 
-    // ---- 1. stage the weights (16-byte aligned, zero padded rows)
-    {
-        float *flat = reinterpret_cast<float *>(&S);
-        constexpr int kWeightFloats = (int)(offsetof(Smem, table) / sizeof(float));
-        for (int i = tid; i < kWeightFloats; i += kThreads) flat[i] = 0.f;
-        if (tid < kRowStride) S.table[R_ONE][tid] = 1.f;
-        for (int i = tid; i < kSlice * kCluster; i += kThreads) S.partial[i] = 0.f;
-        __syncthreads();
-        const float *prm = job.params;
-        for (int i = tid; i < P; i += kThreads) {
-            float val = prm[i];
-            if (i < OB0) S.w0[i / 2][i & 1] = val;
-            else if (i < OW1) S.b[0][i - OB0] = val;
-            else if (i < OW4) {
-                int q = i - OW1, l = q / kHidden, r = q - l * kHidden;
-                if (r < H * H) S.wh[l][r / H][r % H] = val;
-                else S.b[l + 1][r - H * H] = val;
-            } else if (i < OB4) S.w4[i - OW4] = val;
-            else S.b4[0] = val;
+    // ---- compute warps: the first batch rows are requested before the weights are staged
+    const int32_t *idx_row = job.idx ? job.idx + (seq % job.idx_rows) * (long long)job.idx_stride : nullptr;
+    float x0 = 0.f, x1 = 0.f, y = 0.f;
+    auto fetch_sample = [&](int chunk0) {
+        const int b = chunk0 + cta * kLanes + lane;
+        x0 = 0.f; x1 = 0.f; y = 0.f;
+        if (compute && b < B) {
+            const long long s = idx_row ? (long long)idx_row[b] : (long long)b;
+            const float2 xv = *reinterpret_cast<const float2 *>(job.x + 2 * s);
+            x0 = xv.x; x1 = xv.y;
+            if (mode != DDPB_MODE_FWD) y = job.y[s];
         }
-        __syncthreads();
+    };
+    fetch_sample(0);
+    stage_weights(S, job.params, tid);
+    __syncthreads();
+
+    if (!compute) {
+        if (mode == DDPB_MODE_FWD) return;
+        // ================= optimizer warps =================
+        cluster.sync();                                   // partials of all eight CTAs are published
+        if (owner) {
+            float total = 0.f;
+#pragma unroll
+            for (int c = 0; c < kCluster; ++c) total += cluster.map_shared_rank(S.partial, c)[own];
+            if (own == P) {
+                job.grads[P] = total;                                        // sum (o-t)^2 over the local batch
+                if (job.loss_ring) job.loss_ring[seq % job.loss_ring_n] = total / (float)B;
+            } else {
+                job.grads[own] = total;
+                if (mode == DDPB_MODE_STEP) {
+                    const float g = total;
+                    if (job.opt == DDPB_OPT_ADAM) {
+                        // torch:optim/adam.py:457 (lerp), :476 (mul, addcmul), :545 (denom), :547 (addcdiv);
+                        // bias.x = -(lr / (1 - beta1^t)), bias.y = sqrt(1 - beta2^t): host table (:531-536)
+                        const float w1 = (float)(1.0 - job.beta1), b2 = (float)job.beta2;
+                        const float w2 = (float)(1.0 - job.beta2), eps = (float)job.eps;
+                        const float m_new = __fmaf_rn(w1, __fsub_rn(g, m_old), m_old);
+                        const float v_new = __fadd_rn(__fmul_rn(v_old, b2), __fmul_rn(__fmul_rn(w2, g), g));
+                        const float denom = __fadd_rn(__fdiv_rn(__fsqrt_rn(v_new), bias.y), eps);
+                        job.params[own] = __fadd_rn(p_old, __fmul_rn(bias.x, __fdiv_rn(m_new, denom)));
+                        job.m[own] = m_new;
+                        job.v[own] = v_new;
+                    } else {
+                        // torch:optim/sgd.py _single_tensor_sgd: buf = g (first step) | momentum*buf + g
+                        float d = g;
+                        if (job.momentum != 0.0) {
+                            const float mo = (float)job.momentum;
+                            d = (step == 0) ? g : __fadd_rn(__fmul_rn(m_old, mo), g);
+                            job.m[own] = d;
+                        }
+                        job.params[own] = __fsub_rn(p_old, __fmul_rn((float)job.lr, d));
+                    }
+                }
+            }
+        }
+        if (cta == 0 && tid == kComputeThreads) {          // advance the device-resident counters
+            job.state->seq = seq + 1;
+            if (mode == DDPB_MODE_STEP) job.state->step = step + 1;
+        }
+        cluster_rendezvous_relaxed();
+        return;
     }
 
-    // gradient rows of the (up to three) parameters this thread accumulates
+    // ================= compute warps =================
     int row_dz[3], row_a[3];
     float gacc[3] = {0.f, 0.f, 0.f};
 #pragma unroll
     for (int r = 0; r < 3; ++r) {
-        int i = tid + r * kThreads;
+        const int i = tid + r * kComputeThreads;
         row_dz[r] = R_ONE; row_a[r] = R_ONE;
         if (i < P) rows_of_param(i, row_dz[r], row_a[r]);
     }
     float sq_acc = 0.f;
     const float norm = (float)(2.0 / (double)B);        // mse_loss_backward: 2/numel
-    const int32_t *idx_row = job.idx ? job.idx + (seq % job.idx_rows) * (long long)job.idx_stride : nullptr;
 
     for (int chunk0 = 0; chunk0 < B; chunk0 += kChunk) {
-        const int first = chunk0 + cta * kLanes;
-        const bool cta_has_samples = first < B;          // uniform per CTA
+        const bool cta_has_samples = chunk0 + cta * kLanes < B;          // uniform per CTA
+        const bool valid = chunk0 + cta * kLanes + lane < B;
         if (cta_has_samples) {
-            const int b = first + lane;
-            const bool valid = b < B;
-            float x0 = 0.f, x1 = 0.f, y = 0.f;
-            if (valid) {
-                const long long s = idx_row ? (long long)idx_row[b] : (long long)b;
-                const float2 xv = *reinterpret_cast<const float2 *>(job.x + 2 * s);
-                x0 = xv.x; x1 = xv.y;
-                if (mode != DDPB_MODE_FWD) y = job.y[s];
-            }
-            // ---- forward, one sample per lane
-            float a0[H], a1[H], a2[H], a3[H];
-            unsigned k0 = 0, k1, k2, k3;
+            // neurons owned by this warp in every layer: warp, warp+4, warp+8 (the last: warps 0,1 only)
+            unsigned mask[4] = {0u, 0u, 0u, 0u};          // bit i: pre-activation of owned neuron i > 0
+            float cur[H];
+            // ---- layer 0 (2 -> H)
+            if (warp == 0) { S.table[R_IN][lane] = x0; S.table[R_IN + 1][lane] = x1; }
 #pragma unroll
-            for (int j = 0; j < H; ++j) {
-                float acc = S.b[0][j];
-                acc = fmaf(S.w0[j][0], x0, acc);
-                acc = fmaf(S.w0[j][1], x1, acc);
-                k0 |= (acc > 0.f ? 1u : 0u) << j;
-                a0[j] = lrelu(acc);
-            }
-            hidden_fwd(S, 0, a0, a1, k1);
-            asm volatile("" ::: "memory");
-            hidden_fwd(S, 1, a1, a2, k2);
-            asm volatile("" ::: "memory");
-            hidden_fwd(S, 2, a2, a3, k3);
-            float out = S.b4[0];
-            {
-                float w[kWRow];
-                load_row(S.w4, w);
-#pragma unroll
-                for (int k = 0; k < H; ++k) out = fmaf(w[k], a3[k], out);
-            }
-            if (mode == DDPB_MODE_FWD) {
-                if (valid && warp == 0) job.out[b] = out;
-                continue;
-            }
-            put<R_IN + 0>(S, warp, lane, x0);
-            put<R_IN + 1>(S, warp, lane, x1);
-            put_vec<R_ACT + 0 * H>(S, warp, lane, a0);
-            put_vec<R_ACT + 1 * H>(S, warp, lane, a1);
-            put_vec<R_ACT + 2 * H>(S, warp, lane, a2);
-            put_vec<R_ACT + 3 * H>(S, warp, lane, a3);
-
-            // ---- loss and backward.  The barrier stops nvcc from keeping all 340 forward
-            // weights live in registers for reuse here (it spills otherwise); reloading a
-            // 48-byte row from shared memory is cheaper than a local-memory round trip.
-            asm volatile("" ::: "memory");
-            const float diff = valid ? out - y : 0.f;
-            if (warp == 0) {
-                float sq = diff * diff;
-#pragma unroll
-                for (int off = 16; off > 0; off >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, off);
-                sq_acc += sq;
-            }
-            const float dz4 = norm * diff;
-            put<R_DZ + 4 * H>(S, warp, lane, dz4);
-            float d3[H], d2[H], d1[H], d0[H];
-            {
-                float w[kWRow];
-                load_row(S.w4, w);
-#pragma unroll
-                for (int k = 0; k < H; ++k) {
-                    float g = fmaf(dz4, w[k], 0.f);
-                    d3[k] = ((k3 >> k) & 1u) ? g : g * kSlope;
+            for (int i = 0; i < kOwned; ++i) {
+                const int j = warp + 4 * i;
+                if (j < H) {
+                    float acc = S.b[0][j];
+                    acc = fmaf(S.w0[j][0], x0, acc);
+                    acc = fmaf(S.w0[j][1], x1, acc);
+                    mask[0] |= (acc > 0.f ? 1u : 0u) << i;
+                    S.table[R_ACT + j][lane] = lrelu(acc);
                 }
             }
-            put_vec<R_DZ + 3 * H>(S, warp, lane, d3);
-            hidden_bwd(S, 2, d3, k2, d2);
-            put_vec<R_DZ + 2 * H>(S, warp, lane, d2);
-            asm volatile("" ::: "memory");
-            hidden_bwd(S, 1, d2, k1, d1);
-            put_vec<R_DZ + 1 * H>(S, warp, lane, d1);
-            asm volatile("" ::: "memory");
-            hidden_bwd(S, 0, d1, k0, d0);
-            put_vec<R_DZ + 0 * H>(S, warp, lane, d0);
+            compute_barrier();
+            // ---- layers 1..3 (H -> H)
+#pragma unroll
+            for (int l = 0; l < 3; ++l) {
+                read_rows(S, R_ACT + l * H, lane, cur);
+#pragma unroll
+                for (int i = 0; i < kOwned; ++i) {
+                    const int j = warp + 4 * i;
+                    if (j < H) {
+                        float w[kWRow];
+                        load_row(S.wh[l][j], w);
+                        float acc = S.b[l + 1][j];
+#pragma unroll
+                        for (int k = 0; k < H; ++k) acc = fmaf(w[k], cur[k], acc);
+                        mask[l + 1] |= (acc > 0.f ? 1u : 0u) << i;
+                        S.table[R_ACT + (l + 1) * H + j][lane] = lrelu(acc);
+                    }
+                }
+                compute_barrier();
+            }
+            // ---- layer 4 (H -> 1): every warp computes it, all of them need the loss gradient
+            read_rows(S, R_ACT + 3 * H, lane, cur);
+            float out = S.b4[0];
+            float w4[kWRow];
+            load_row(S.w4, w4);
+#pragma unroll
+            for (int k = 0; k < H; ++k) out = fmaf(w4[k], cur[k], out);
+            if (mode == DDPB_MODE_FWD) {
+                if (valid && warp == 0) job.out[chunk0 + cta * kLanes + lane] = out;
+            } else {
+                // ---- loss, then backward: warp w produces dz for the neurons it owns
+                const float diff = valid ? out - y : 0.f;
+                const float dz4 = norm * diff;
+                if (warp == 0) {
+                    float sq = diff * diff;
+#pragma unroll
+                    for (int off = 16; off > 0; off >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, off);
+                    sq_acc += sq;
+                    S.table[R_DZ + 4 * H][lane] = dz4;
+                }
+#pragma unroll
+                for (int i = 0; i < kOwned; ++i) {
+                    const int k = warp + 4 * i;
+                    if (k < H) {
+                        const float g = fmaf(dz4, w4[k], 0.f);
+                        S.table[R_DZ + 3 * H + k][lane] = ((mask[3] >> i) & 1u) ? g : g * kSlope;
+                    }
+                }
+                compute_barrier();
+#pragma unroll
+                for (int l = 2; l >= 0; --l) {            // through W_{l+1}: dz_{l+1} -> dz_l
+                    read_rows(S, R_DZ + (l + 1) * H, lane, cur);
+#pragma unroll
+                    for (int i = 0; i < kOwned; ++i) {
+                        const int k = warp + 4 * i;
+                        if (k < H) {
+                            float w[kWRow];
+                            load_row(S.wt[l][k], w);
+                            float s = 0.f;
+#pragma unroll
+                            for (int j = 0; j < H; ++j) s = fmaf(cur[j], w[j], s);
+                            S.table[R_DZ + l * H + k][lane] = ((mask[l] >> i) & 1u) ? s : s * kSlope;
+                        }
+                    }
+                    compute_barrier();
+                }
+            }
         }
-        if (mode == DDPB_MODE_FWD) continue;
-        __syncthreads();
-        // ---- weight gradients of this CTA's 32 samples
+        if (mode == DDPB_MODE_FWD) {
+            if (chunk0 + kChunk < B) { compute_barrier(); fetch_sample(chunk0 + kChunk); }
+            continue;
+        }
+        // ---- weight gradients of this CTA's 32 samples (the table is complete: last barrier above)
         if (cta_has_samples) {
 #pragma unroll
             for (int r = 0; r < 3; ++r) {
-                if (tid + r * kThreads < P) {
+                if (tid + r * kComputeThreads < P) {
                     const float4 *pd = reinterpret_cast<const float4 *>(S.table[row_dz[r]]);
                     const float4 *pa = reinterpret_cast<const float4 *>(S.table[row_a[r]]);
-                    float s = 0.f;
+                    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
 #pragma unroll
                     for (int c = 0; c < kLanes / 4; ++c) {
-                        float4 d = pd[c], a = pa[c];
-                        s = fmaf(d.x, a.x, s); s = fmaf(d.y, a.y, s);
-                        s = fmaf(d.z, a.z, s); s = fmaf(d.w, a.w, s);
+                        const float4 d = pd[c], a = pa[c];
+                        s0 = fmaf(d.x, a.x, s0); s1 = fmaf(d.y, a.y, s1);
+                        s2 = fmaf(d.z, a.z, s2); s3 = fmaf(d.w, a.w, s3);
                     }
-                    gacc[r] += s;
+                    gacc[r] += (s0 + s1) + (s2 + s3);
                 }
             }
         }
-        __syncthreads();
+        if (chunk0 + kChunk < B) {                         // another pass: the table is about to be overwritten
+            compute_barrier();
+            fetch_sample(chunk0 + kChunk);
+        }
     }
     if (mode == DDPB_MODE_FWD) return;
 
-    // ---- 2. publish the partials, reduce my slice across the cluster
+    // ---- publish the partials; the optimizer warps of the cluster take it from here
 #pragma unroll
     for (int r = 0; r < 3; ++r)
-        if (tid + r * kThreads < P) S.partial[tid + r * kThreads] = gacc[r];
+        if (tid + r * kComputeThreads < P) S.partial[tid + r * kComputeThreads] = gacc[r];
     if (tid == 0) S.partial[P] = sq_acc;
     cluster.sync();
-
-    if (owner) {
-        float total = 0.f;
-#pragma unroll
-        for (int c = 0; c < kCluster; ++c) total += cluster.map_shared_rank(S.partial, c)[own];
-        if (own == P) {
-            job.grads[P] = total;                                        // sum (o-t)^2 over the local batch
-            if (job.loss_ring) job.loss_ring[seq % job.loss_ring_n] = total / (float)B;
-        } else {
-            job.grads[own] = total;
-            if (mode == DDPB_MODE_STEP) {
-                const float g = total;
-                if (job.opt == DDPB_OPT_ADAM) {
-                    // torch:optim/adam.py:457 (lerp), :476 (mul, addcmul), :531-536 (bias corrections
-                    // in double), :545 (denom), :547 (addcdiv)
-                    const double bc1 = 1.0 - b1pow * job.beta1;
-                    const double bc2 = 1.0 - b2pow * job.beta2;
-                    const float neg_step = (float)(-(job.lr / bc1));
-                    const float bc2_sqrt = (float)sqrt(bc2);
-                    const float w1 = (float)(1.0 - job.beta1), b2 = (float)job.beta2;
-                    const float w2 = (float)(1.0 - job.beta2), eps = (float)job.eps;
-                    const float m_new = __fmaf_rn(w1, __fsub_rn(g, m_old), m_old);
-                    const float v_new = __fadd_rn(__fmul_rn(v_old, b2), __fmul_rn(__fmul_rn(w2, g), g));
-                    const float denom = __fadd_rn(__fdiv_rn(__fsqrt_rn(v_new), bc2_sqrt), eps);
-                    job.params[own] = __fadd_rn(p_old, __fmul_rn(neg_step, __fdiv_rn(m_new, denom)));
-                    job.m[own] = m_new;
-                    job.v[own] = v_new;
-                } else {
-                    // torch:optim/sgd.py _single_tensor_sgd: buf = g (first step) | momentum*buf + g
-                    float d = g;
-                    if (job.momentum != 0.0) {
-                        const float mo = (float)job.momentum;
-                        d = (step == 0) ? g : __fadd_rn(__fmul_rn(m_old, mo), g);
-                        job.m[own] = d;
-                    }
-                    job.params[own] = __fsub_rn(p_old, __fmul_rn((float)job.lr, d));
-                }
-            }
-        }
-    }
-    cluster.sync();   // nobody leaves while a peer may still read its partials
-
-    // ---- 3. advance the device-resident counters
-    if (cta == 0 && tid == 0 && job.state) {
-        job.state->seq = seq + 1;
-        if (mode == DDPB_MODE_STEP) {
-            job.state->step = step + 1;
-            job.state->beta1_pow = b1pow * job.beta1;
-            job.state->beta2_pow = b2pow * job.beta2;
-        }
-    }
+    cluster_rendezvous_relaxed();
 }
 
 }  // namespace
@@ -401,7 +381,8 @@ DDPB_API int ddpb_toy_step(const ddpb_toy_job *jobs, int njobs, void *stream) {
         else DDPB_REQUIRE(q.y && q.grads && q.state, "ddpb_toy_step: job %d: y, grads and state are required", j);
         if (q.mode == DDPB_MODE_STEP) {
             DDPB_REQUIRE(q.opt == DDPB_OPT_ADAM || q.opt == DDPB_OPT_SGD, "ddpb_toy_step: job %d: unknown optimizer", j);
-            DDPB_REQUIRE(q.m && (q.opt == DDPB_OPT_SGD || q.v), "ddpb_toy_step: job %d: optimizer state missing", j);
+            DDPB_REQUIRE(q.m && (q.opt == DDPB_OPT_SGD || (q.v && q.bias_table && q.bias_table_n >= 1)),
+                         "ddpb_toy_step: job %d: optimizer state (m, v, bias table) missing", j);
         }
         if (q.loss_ring) DDPB_REQUIRE(q.loss_ring_n >= 1, "ddpb_toy_step: job %d: empty loss ring", j);
         if (q.idx) DDPB_REQUIRE(q.idx_rows >= 1 && q.idx_stride >= q.B, "ddpb_toy_step: job %d: index rows too short", j);

@@ -18,9 +18,6 @@ What the reference's wrapper does with ~30 tensors, hooks and a C++ Reducer
 There is no fallback to PyTorch modules: a model this package has no kernels for, or a
 CPU-resident module, raises.
 """
-import ctypes
-
-import numpy as np
 import torch
 import torch.distributed as dist
 
@@ -131,9 +128,7 @@ class ToyBackend:
                 p.grad = self.grads[off:off + n].view(p.shape)
                 _OWNERS[id(p)] = self
                 off += n
-            init = np.zeros(4, np.int64)
-            init[2:] = np.array([1.0, 1.0], np.float64).view(np.int64)
-            self.state = torch.from_numpy(init).to(dev)
+            self.state = torch.zeros(4, dtype=torch.int64, device=dev)       # ddpb_opt_state {step, seq, ...}
             self.loss_ring = torch.zeros(LOSS_RING, dtype=torch.float32, device=dev)
             self.loss_host = torch.zeros(LOSS_RING, dtype=torch.float32, pin_memory=True)
             self.m = self.v = None
@@ -185,6 +180,9 @@ class ToyBackend:
         if kind == _lib.OPT_ADAM:
             j.beta1, j.beta2 = hyper["betas"]
             j.eps = hyper["eps"]
+            table = _lib.adam_bias_table(hyper["lr"], *hyper["betas"])
+            self.bias_table = torch.from_numpy(table).to(self.device)
+            j.bias_table, j.bias_table_n = self.bias_table.data_ptr(), table.shape[0]
         else:
             j.beta1 = j.beta2 = 1.0
             j.momentum = hyper["momentum"]
@@ -275,8 +273,9 @@ class ToyBackend:
         scale = 1.0 / self.world
         if self.opt_kind == _lib.OPT_ADAM:
             _lib.check(lib.ddpb_fused_avg_adam_dev(self.grads.data_ptr(), self.params.data_ptr(), self.m.data_ptr(),
-                                                   self.v.data_ptr(), self.P, scale, h["lr"], h["betas"][0],
-                                                   h["betas"][1], h["eps"], self.state.data_ptr(), 1, stream),
+                                                   self.v.data_ptr(), self.P, scale, h["betas"][0], h["betas"][1],
+                                                   h["eps"], self.job.bias_table, self.job.bias_table_n,
+                                                   self.state.data_ptr(), 1, stream),
                        "ddpb_fused_avg_adam_dev")
             self.engine.launches += 2
         else:

@@ -80,15 +80,20 @@ enum { DDPB_OPT_ADAM = 0, DDPB_OPT_SGD = 1 };
 typedef struct ddpb_opt_state {
     long long step;    /* optimizer steps applied so far */
     long long seq;     /* gradient evaluations so far (selects loss slot / index row) */
-    double beta1_pow;  /* beta1^step (1.0 at step 0) */
-    double beta2_pow;  /* beta2^step */
+    long long reserved[2];
 } ddpb_opt_state;
+
+/* Adam's bias corrections are Python doubles in torch (torch:optim/adam.py:531-536).  The host
+ * layer tabulates them once per optimizer: entry t-1 = { (float)-(lr / (1 - beta1^t)),
+ * (float)sqrt(1 - beta2^t) } for step t = 1..n; the table must run until both have converged
+ * (t > n reuses entry n-1).  Kernels index it with the device-resident step counter. */
 
 typedef struct ddpb_toy_job {
     float *params;            /* [371] flat, module.parameters() order: W0,b0,...,W4,b4 */
     float *grads;             /* [372] flat gradient bucket; element 371 carries sum (o-t)^2 */
     float *m, *v;             /* Adam moments [371] (m = SGD momentum buffer); STEP only */
     ddpb_opt_state *state;    /* device counters */
+    const float *bias_table;  /* Adam: [bias_table_n][2] bias-correction scalars (see above), 8-byte aligned */
     float *loss_ring;         /* [loss_ring_n] mean-loss slots, slot = seq % loss_ring_n */
     const float *x;           /* [B,2] batch, or the whole dataset when idx != NULL */
     const float *y;           /* [B,1] targets, or the whole dataset */
@@ -99,6 +104,7 @@ typedef struct ddpb_toy_job {
     int32_t opt;              /* DDPB_OPT_* */
     int32_t loss_ring_n;
     int32_t idx_rows, idx_stride;
+    int32_t bias_table_n, reserved;
     double lr, beta1, beta2, eps, momentum;
 } ddpb_toy_job;
 
@@ -113,9 +119,11 @@ int ddpb_toy_step(const ddpb_toy_job *jobs /* host */, int njobs, void *stream);
 int ddpb_fused_avg_adam(const float *bucket, float *p, float *m, float *v, int64_t n,
                         float grad_scale, double lr, double beta1, double beta2, double eps,
                         int64_t step, void *stream);
-/* Same with device-resident counters (graph-replayable); advances state->step. */
+/* Same with the device-resident step counter and the bias table (graph-replayable);
+ * advance != 0 increments state->step afterwards. */
 int ddpb_fused_avg_adam_dev(const float *bucket, float *p, float *m, float *v, int64_t n,
-                            float grad_scale, double lr, double beta1, double beta2, double eps,
+                            float grad_scale, double beta1, double beta2, double eps,
+                            const float *bias_table, int bias_table_n,
                             ddpb_opt_state *state, int advance, void *stream);
 /* SGD with optional momentum (north_star lists it beside Adam; torch:optim/sgd.py). */
 int ddpb_fused_avg_sgd(const float *bucket, float *p, float *buf, int64_t n, float grad_scale,

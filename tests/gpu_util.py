@@ -14,9 +14,17 @@ def dev(a, dtype=torch.float32):
 
 
 def new_state():
-    init = np.zeros(4, np.int64)
-    init[2:] = np.array([1.0, 1.0], np.float64).view(np.int64)
-    return torch.from_numpy(init).cuda()
+    return torch.zeros(4, dtype=torch.int64, device="cuda")
+
+
+_TABLES = {}
+
+
+def bias_table(lr=1e-3, beta1=0.9, beta2=0.999):
+    key = (lr, beta1, beta2)
+    if key not in _TABLES:
+        _TABLES[key] = torch.from_numpy(_lib.adam_bias_table(lr, beta1, beta2)).cuda()
+    return _TABLES[key]
 
 
 class ToyHarness:
@@ -33,6 +41,8 @@ class ToyHarness:
         j.params, j.grads, j.m, j.v = (t.data_ptr() for t in (self.params, self.grads, self.m, self.v))
         j.state, j.loss_ring, j.loss_ring_n = self.state.data_ptr(), self.ring.data_ptr(), ring
         j.opt, j.lr, j.beta1, j.beta2, j.eps, j.momentum = opt, lr, 0.9, 0.999, 1e-8, momentum
+        self.table = bias_table(lr)
+        j.bias_table, j.bias_table_n = self.table.data_ptr(), self.table.shape[0]
         j.idx_rows, j.idx_stride = 1, 0
         self.seq = 0
         self.keep = None

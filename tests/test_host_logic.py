@@ -26,8 +26,8 @@ def test_library_exports_every_declared_symbol(native_lib):
 
 
 def test_struct_layout_matches_header():
-    # 10 pointers + 6 int32 + 5 doubles, naturally aligned
-    assert ctypes.sizeof(_lib.ToyJob) == 10 * 8 + 6 * 4 + 5 * 8
+    # 11 pointers + 8 int32 + 5 doubles, naturally aligned
+    assert ctypes.sizeof(_lib.ToyJob) == 11 * 8 + 8 * 4 + 5 * 8
     assert ctypes.sizeof(_lib.OptState) == 32
 
 
@@ -145,3 +145,11 @@ def test_no_cpu_fallback():
         b200.DistributedDataParallel(b200.ToyModel(), device_ids=None)
     with pytest.raises(RuntimeError):
         b200.ToyModel()(torch.zeros(4, 2))
+
+
+def test_adam_bias_table_is_torchs_python_arithmetic():
+    table = _lib.adam_bias_table(1e-3, 0.9, 0.999)
+    for t in (1, 2, 10, 999, 5000, table.shape[0]):
+        bc1, bc2 = 1 - 0.9 ** t, 1 - 0.999 ** t                   # torch:optim/adam.py:531-536
+        assert table[t - 1, 0] == np.float32(-(1e-3 / bc1)) and table[t - 1, 1] == np.float32(bc2 ** 0.5)
+    assert table[-1].tolist() == [np.float32(-1e-3), 1.0]        # converged: later steps reuse the last row
