@@ -56,6 +56,10 @@ _SIGNATURES = {
     "ddpb_comm_destroy": (c_int, [c_void_p]),
     "ddpb_broadcast_f32": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_void_p]),
     "ddpb_allreduce_sum_f32": (c_int, [c_void_p, c_void_p, c_int64, c_void_p]),
+    "ddpb_graph_begin": (c_int, [c_void_p]),
+    "ddpb_graph_end": (c_int, [c_void_p, c_void_p]),
+    "ddpb_graph_launch": (c_int, [c_void_p, c_void_p]),
+    "ddpb_graph_destroy": (c_int, [c_void_p]),
     "ddpb_stream_sync": (c_int, [c_void_p]),
     "ddpb_memcpy_h2d_async": (c_int, [c_void_p, c_void_p, c_int64, c_void_p]),
     "ddpb_memcpy_d2h_async": (c_int, [c_void_p, c_void_p, c_int64, c_void_p]),

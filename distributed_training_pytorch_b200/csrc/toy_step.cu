@@ -78,7 +78,24 @@ struct __align__(16) Smem {
     float partial[kSlice * kCluster];
 };
 
+#ifdef DDPB_TIMELINE
+// Development aid (tools/toy_timeline.py): per-phase SM clock stamps written through job.out.
+#define DDPB_STAMP(slot)                                                                              \
+    do {                                                                                              \
+        if (lane == 0 && job.out) reinterpret_cast<long long *>(job.out)[(blockIdx.y * kCluster + cta) * 64 + warp * 8 + (slot)] = clock64(); \
+    } while (0)
+#else
+#define DDPB_STAMP(slot) do { } while (0)
+#endif
+
 __device__ __forceinline__ float lrelu(float z) { return z > 0.f ? z : z * kSlope; }
+
+// seq % n without a 64-bit division: a mask when n is a power of two (exact for ever), else a
+// 32-bit modulo of the low word (exact for the first 2^32 evaluations).
+__device__ __forceinline__ unsigned wrap_index(long long seq, int n) {
+    const unsigned u = (unsigned)n, lo = (unsigned)seq;
+    return (u & (u - 1)) == 0 ? (lo & (u - 1)) : lo % u;
+}
 
 __device__ __forceinline__ void compute_barrier() { asm volatile("bar.sync 1, %0;" ::"n"(kComputeThreads) : "memory"); }
 
@@ -142,6 +159,7 @@ toy_step_kernel(const __grid_constant__ JobList jl) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int B = job.B, mode = job.mode;
     const bool compute = tid < kComputeThreads;
+    DDPB_STAMP(0);
     const long long seq = job.state ? job.state->seq : 0;
 
     // ---- optimizer warps: everything they need from HBM is requested before anything else
@@ -164,7 +182,7 @@ toy_step_kernel(const __grid_constant__ JobList jl) {
     }
 
     // ---- compute warps: the first batch rows are requested before the weights are staged
-    const int32_t *idx_row = job.idx ? job.idx + (seq % job.idx_rows) * (long long)job.idx_stride : nullptr;
+    const int32_t *idx_row = job.idx ? job.idx + (long long)wrap_index(seq, job.idx_rows) * job.idx_stride : nullptr;
     float x0 = 0.f, x1 = 0.f, y = 0.f;
     auto fetch_sample = [&](int chunk0) {
         const int b = chunk0 + cta * kLanes + lane;
@@ -179,18 +197,20 @@ toy_step_kernel(const __grid_constant__ JobList jl) {
     fetch_sample(0);
     stage_weights(S, job.params, tid);
     __syncthreads();
+    DDPB_STAMP(1);
 
     if (!compute) {
         if (mode == DDPB_MODE_FWD) return;
         // ================= optimizer warps =================
         cluster.sync();                                   // partials of all eight CTAs are published
+        DDPB_STAMP(2);
         if (owner) {
             float total = 0.f;
 #pragma unroll
             for (int c = 0; c < kCluster; ++c) total += cluster.map_shared_rank(S.partial, c)[own];
             if (own == P) {
                 job.grads[P] = total;                                        // sum (o-t)^2 over the local batch
-                if (job.loss_ring) job.loss_ring[seq % job.loss_ring_n] = total / (float)B;
+                if (job.loss_ring) job.loss_ring[wrap_index(seq, job.loss_ring_n)] = total / (float)B;
             } else {
                 job.grads[own] = total;
                 if (mode == DDPB_MODE_STEP) {
@@ -223,7 +243,9 @@ toy_step_kernel(const __grid_constant__ JobList jl) {
             job.state->seq = seq + 1;
             if (mode == DDPB_MODE_STEP) job.state->step = step + 1;
         }
+        DDPB_STAMP(3);
         cluster_rendezvous_relaxed();
+        DDPB_STAMP(4);
         return;
     }
 
@@ -280,6 +302,7 @@ toy_step_kernel(const __grid_constant__ JobList jl) {
                 compute_barrier();
             }
             // ---- layer 4 (H -> 1): every warp computes it, all of them need the loss gradient
+            DDPB_STAMP(2);
             read_rows(S, R_ACT + 3 * H, lane, cur);
             float out = S.b4[0];
             float w4[kWRow];
@@ -332,6 +355,7 @@ toy_step_kernel(const __grid_constant__ JobList jl) {
             continue;
         }
         // ---- weight gradients of this CTA's 32 samples (the table is complete: last barrier above)
+        DDPB_STAMP(3);
         if (cta_has_samples) {
 #pragma unroll
             for (int r = 0; r < 3; ++r) {
@@ -361,8 +385,11 @@ toy_step_kernel(const __grid_constant__ JobList jl) {
     for (int r = 0; r < 3; ++r)
         if (tid + r * kComputeThreads < P) S.partial[tid + r * kComputeThreads] = gacc[r];
     if (tid == 0) S.partial[P] = sq_acc;
+    DDPB_STAMP(4);
     cluster.sync();
+    DDPB_STAMP(5);
     cluster_rendezvous_relaxed();
+    DDPB_STAMP(6);
 }
 
 }  // namespace

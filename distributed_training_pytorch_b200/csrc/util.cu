@@ -48,3 +48,34 @@ DDPB_API int ddpb_memcpy_d2h_async(void *dst_host, const void *src_dev, int64_t 
     DDPB_CUDA(cudaMemcpyAsync(dst_host, src_dev, (size_t)bytes, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
     return 0;
 }
+
+// ---- CUDA graphs: a launch-bound inner loop (thousands of 5 us steps) is captured once and
+// replayed; the kernels read their step/row counters from device memory, so a replay needs no
+// new arguments.
+DDPB_API int ddpb_graph_begin(void *stream) {
+    DDPB_CUDA(cudaStreamBeginCapture((cudaStream_t)stream, cudaStreamCaptureModeThreadLocal));
+    return 0;
+}
+
+DDPB_API int ddpb_graph_end(void *stream, void **graph_exec_out) {
+    DDPB_REQUIRE(graph_exec_out != nullptr, "ddpb_graph_end: null output");
+    cudaGraph_t graph = nullptr;
+    DDPB_CUDA(cudaStreamEndCapture((cudaStream_t)stream, &graph));
+    cudaGraphExec_t exec = nullptr;
+    cudaError_t e = cudaGraphInstantiate(&exec, graph, 0);
+    cudaGraphDestroy(graph);
+    if (e != cudaSuccess) return ddpb::cuda_fail(e, "cudaGraphInstantiate", __FILE__, __LINE__);
+    *graph_exec_out = exec;
+    return 0;
+}
+
+DDPB_API int ddpb_graph_launch(void *graph_exec, void *stream) {
+    DDPB_REQUIRE(graph_exec != nullptr, "ddpb_graph_launch: null graph");
+    DDPB_CUDA(cudaGraphLaunch((cudaGraphExec_t)graph_exec, (cudaStream_t)stream));
+    return 0;
+}
+
+DDPB_API int ddpb_graph_destroy(void *graph_exec) {
+    if (graph_exec) DDPB_CUDA(cudaGraphExecDestroy((cudaGraphExec_t)graph_exec));
+    return 0;
+}

@@ -147,6 +147,15 @@ int ddpb_stream_sync(void *stream);
 int ddpb_memcpy_h2d_async(void *dst_dev, const void *src_host, int64_t bytes, void *stream);
 int ddpb_memcpy_d2h_async(void *dst_host, const void *src_dev, int64_t bytes, void *stream);
 
+/* ---- CUDA graphs --------------------------------------------------------------- */
+/* The reference drives 1000 iterations from Python (demo.py:88-129).  Steps whose inputs are
+ * already in HBM can instead be captured once (begin ... launches on `stream` ... end) and
+ * replayed: every kernel above takes its step / row counters from ddpb_opt_state. */
+int ddpb_graph_begin(void *stream);
+int ddpb_graph_end(void *stream, void **graph_exec_out);
+int ddpb_graph_launch(void *graph_exec, void *stream);
+int ddpb_graph_destroy(void *graph_exec);
+
 #ifdef __cplusplus
 }
 #endif
