@@ -6,22 +6,27 @@
 //   loss.backward()        autograd + DDP reducer hooks, demo.py:107       (~45)
 //   optimizer.step()       optim.Adam foreach path, demo.py:110            (~10)
 // Here it is ONE launch for all models of the process: a thread-block cluster of 8 CTAs
-// per model (blockIdx.y = model).  At this size (1 MFLOP, 10 KB) only latency matters:
-// ncu of the first version (profiles/r01_v0_*) showed one warp per scheduler crawling
-// through a 1900-instruction dependent chain (IPC 0.14).  This version shortens the chain:
+// per model (blockIdx.y = model).  At this size (1 MFLOP, 10 KB) only latency matters; the
+// structure below is the result of two measured iterations (profiles/r01_v0_*, r01_v2_*:
+// ncu stall samples and an in-kernel clock64 timeline, tools/toy_timeline.py):
 //
 //   * CTA c owns samples [32c, 32c+32) of the batch, one sample per lane.  Its four compute
-//     warps split each layer's OUTPUT neurons (warp w owns neurons w, w+4, w+8): a layer is
-//     <= 30 FMAs per warp, the activations meet in a shared-memory table
-//     ([84 rows][32 samples]: inputs, activations, pre-activation gradients), one named
-//     barrier per layer.  The same table is the operand of the weight-gradient contraction
-//     dW = dZ^T A ([371 x 32] x [32] per CTA), thread t computing parameters t, t+128, t+256
-//     with conflict-free LDS.128 rows and four independent partial sums.
+//     warps split each layer's output neurons (warp w owns neurons 3w..3w+2 of a layer padded
+//     to 12, so every warp runs the same branch-free code and its three FMA chains
+//     interleave).  Activations and pre-activation gradients meet in a shared-memory table
+//     ([100 rows][32 samples]), one named barrier per layer.
+//   * The same table is the operand of the weight-gradient contraction dW = dZ^T A
+//     ([371 x 32] x [32] per CTA): 106 threads each own a 2x2 tile of (dz row, activation
+//     row) pairs, which halves the shared-memory traffic of one-output-per-thread.
+//   * Reduction over the 8 CTAs is push-style: every tile owner stores its partial sums
+//     straight into the inbox of the CTA that owns that parameter slice (distributed shared
+//     memory), one thread per destination then arrives on the destination's mbarrier with
+//     cluster-scope release.  No cluster-wide barrier sits on the critical path (the one
+//     that makes the mbarriers visible is arrived at kernel start and waited for much later).
 //   * Two more warps per CTA are the optimizer: they prefetch p, m, v and the bias-correction
-//     scalars of their 47-parameter slice at kernel start, sleep on the cluster barrier, then
-//     sum the eight per-CTA partials through distributed shared memory in a fixed order
-//     (deterministic) and apply Adam/SGD.  Element 371 of the slice table carries
-//     sum (o-t)^2, i.e. the loss.
+//     scalars of their 47-parameter slice at kernel start, sleep on the mbarrier, sum the
+//     eight inbox rows in a fixed order (deterministic) and apply Adam/SGD.  Element 371 of
+//     the slice table carries sum (o-t)^2, i.e. the loss.
 //
 // Arithmetic order of the per-sample chain (fmaf from the bias, k ascending) and of the
 // optimizer (torch's op order, explicit round-to-nearest intrinsics, no contraction) is
@@ -37,14 +42,14 @@ namespace {
 
 constexpr int H = DDPB_TOY_HIDDEN;
 constexpr int P = DDPB_TOY_PARAMS;
+constexpr int HP = 12;                           // neurons per layer after padding (3 per compute warp)
 constexpr int kCluster = 8;
 constexpr int kComputeThreads = 128;             // 4 warps: the per-sample chain and the weight gradients
 constexpr int kThreads = 192;                    // + 2 optimizer warps
 constexpr int kLanes = 32;                       // samples per CTA and pass
 constexpr int kChunk = kCluster * kLanes;        // samples per cluster pass
-constexpr int kWRow = 12;                        // padded weight row, 3 x float4
 constexpr int kRowStride = 36;                   // floats per table row: 144 B keeps LDS.128 conflict-free
-constexpr int kOwned = 3;                        // neurons per warp and layer (ceil(10/4))
+constexpr int kOwned = HP / 4;                   // neurons per warp and layer
 constexpr float kSlope = 0.01f;                  // nn.LeakyReLU() default
 
 // offsets inside the flat parameter vector (module.parameters() order)
@@ -54,29 +59,38 @@ constexpr int kHidden = H * H + H;               // one hidden layer: W then b
 constexpr int OW4 = OW1 + 3 * kHidden, OB4 = OW4 + H;
 static_assert(OB4 + 1 == P, "flat layout must add up to the parameter count");
 
-// rows of the per-sample table
+// rows of the per-sample table (HP rows per layer; rows of padding neurons hold zeros)
 constexpr int R_IN = 0;                          // x0, x1
-constexpr int R_ACT = 2;                         // act_0 .. act_3 (H rows each)
-constexpr int R_ONE = R_ACT + 4 * H;             // ones (bias gradients)
-constexpr int R_DZ = R_ONE + 1;                  // dz_0 .. dz_3 (H rows each), then dz_4
-constexpr int kRows = R_DZ + 4 * H + 1;
+constexpr int R_ACT = 2;                         // act_0 .. act_3
+constexpr int R_ONE = R_ACT + 4 * HP;            // ones (bias gradients)
+constexpr int R_ZERO = R_ONE + 1;                // zeros (padding operand of 2x2 tiles)
+constexpr int R_DZ = R_ZERO + 1;                 // dz_0 .. dz_3, then dz_4
+constexpr int kRows = R_DZ + 4 * HP + 1;
 constexpr int kSlice = (P + 1 + kCluster - 1) / kCluster;   // 47 values per CTA (371 grads + loss sum)
-static_assert(kSlice <= kThreads - kComputeThreads, "the optimizer warps must cover a slice");
+constexpr int kInboxRow = 48;
+static_assert(kSlice <= kThreads - kComputeThreads && kSlice <= kInboxRow, "the optimizer warps must cover a slice");
+
+// weight-gradient tiles: 3 hidden layers x (5 neuron pairs x 6 input pairs) + layer 0 (5 x 2) + layer 4 (1 x 6)
+constexpr int kTilesHidden = 30, kTilesL0 = 10, kTilesL4 = 6;
+constexpr int kTiles = 3 * kTilesHidden + kTilesL0 + kTilesL4;
+static_assert(kTiles <= kComputeThreads, "one tile per compute thread");
 
 struct JobList {
     ddpb_toy_job jobs[DDPB_MAX_JOBS];
 };
 
 struct __align__(16) Smem {
-    float w0[H][4];            // layer 0: [j][k<2]
-    float wh[3][H][kWRow];     // layers 1..3, [j][k]   (forward: row j)
-    float wt[3][H][kWRow];     // layers 1..3, [k][j]   (backward: column k as a row)
-    float w4[kWRow];           // layer 4
-    float b[4][kWRow];         // biases of layers 0..3
+    float w0[HP][4];           // layer 0: [j][k<2]
+    float wh[3][HP][HP];       // layers 1..3, [j][k]   (forward: row j)
+    float wt[3][HP][HP];       // layers 1..3, [k][j]   (backward: column k as a row)
+    float w4[HP];              // layer 4
+    float b[4][HP];            // biases of layers 0..3
     float b4[4];
     float table[kRows][kRowStride];
-    float partial[kSlice * kCluster];
+    float inbox[kCluster][kInboxRow];   // partial sums pushed by the cluster's CTAs for MY slice
+    unsigned long long mbar;            // counts the 8 "pushed" arrivals
 };
+constexpr int kWeightFloats = (int)(offsetof(Smem, table) / sizeof(float));
 
 #ifdef DDPB_TIMELINE
 // Development aid (tools/toy_timeline.py): per-phase SM clock stamps written through job.out.
@@ -99,14 +113,36 @@ __device__ __forceinline__ unsigned wrap_index(long long seq, int n) {
 
 __device__ __forceinline__ void compute_barrier() { asm volatile("bar.sync 1, %0;" ::"n"(kComputeThreads) : "memory"); }
 
-// Second cluster-barrier phase: pure execution ordering (keeps every CTA's shared memory
-// alive until all remote reads are done), so no release/acquire fence is paid for.
-__device__ __forceinline__ void cluster_rendezvous_relaxed() {
-    asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
-    asm volatile("barrier.cluster.wait.aligned;" ::: "memory");
+__device__ __forceinline__ unsigned smem_addr(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(unsigned long long *bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_addr(bar)), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
 }
 
-__device__ __forceinline__ void load_row(const float *row, float (&w)[kWRow]) {
+// Arrive on the mbarrier of CTA `rank` of this cluster; release at cluster scope publishes the
+// partial sums this CTA stored into that CTA's inbox (cumulative over the preceding bar.sync).
+__device__ __forceinline__ void mbar_arrive_remote(unsigned long long *bar, unsigned rank) {
+    unsigned remote;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(smem_addr(bar)), "r"(rank));
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(remote) : "memory");
+}
+
+__device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned parity) {
+    unsigned done;
+    do {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done) : "r"(smem_addr(bar)), "r"(parity) : "memory");
+    } while (!done);
+}
+
+__device__ __forceinline__ void cluster_arrive() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
+__device__ __forceinline__ void cluster_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
+
+__device__ __forceinline__ void load_row(const float *row, float (&w)[HP]) {
     const float4 *q = reinterpret_cast<const float4 *>(row);
     float4 a = q[0], b = q[1], c = q[2];
     w[0] = a.x; w[1] = a.y; w[2] = a.z; w[3] = a.w;
@@ -114,40 +150,73 @@ __device__ __forceinline__ void load_row(const float *row, float (&w)[kWRow]) {
     w[8] = c.x; w[9] = c.y; w[10] = c.z; w[11] = c.w;
 }
 
-// Read H consecutive table rows of this lane's sample.
+// Read the H real rows of a layer for this lane's sample.
 __device__ __forceinline__ void read_rows(const Smem &S, int row0, int lane, float (&v)[H]) {
 #pragma unroll
     for (int k = 0; k < H; ++k) v[k] = S.table[row0 + k][lane];
 }
 
-// Which table rows produce the gradient of flat parameter i:  grad_i = sum_b dz_row[b] * a_row[b].
-__device__ __forceinline__ void rows_of_param(int i, int &row_dz, int &row_a) {
-    if (i < OW1) {                      // layer 0
-        if (i < OB0) { row_dz = R_DZ + i / 2; row_a = R_IN + (i & 1); }
-        else         { row_dz = R_DZ + (i - OB0); row_a = R_ONE; }
-    } else if (i < OW4) {               // layers 1..3
+// Scatter flat parameter i into the staged (padded, partly transposed) copies.
+__device__ __forceinline__ void stage_param(Smem &S, int i, float val) {
+    if (i < OB0) S.w0[i / 2][i & 1] = val;
+    else if (i < OW1) S.b[0][i - OB0] = val;
+    else if (i < OW4) {
         int q = i - OW1, l = q / kHidden, r = q - l * kHidden;
-        if (r < H * H) { row_dz = R_DZ + (l + 1) * H + r / H; row_a = R_ACT + l * H + r % H; }
-        else           { row_dz = R_DZ + (l + 1) * H + (r - H * H); row_a = R_ONE; }
-    } else {                            // layer 4
-        row_dz = R_DZ + 4 * H;
-        row_a = (i < OB4) ? R_ACT + 3 * H + (i - OW4) : R_ONE;
-    }
+        if (r < H * H) { S.wh[l][r / H][r % H] = val; S.wt[l][r % H][r / H] = val; }
+        else S.b[l + 1][r - H * H] = val;
+    } else if (i < OB4) S.w4[i - OW4] = val;
+    else S.b4[0] = val;
 }
 
-__device__ __forceinline__ void stage_weights(Smem &S, const float *__restrict__ prm, int tid) {
-    for (int i = tid; i < P; i += kThreads) {
-        const float val = prm[i];
-        if (i < OB0) S.w0[i / 2][i & 1] = val;
-        else if (i < OW1) S.b[0][i - OB0] = val;
-        else if (i < OW4) {
-            int q = i - OW1, l = q / kHidden, r = q - l * kHidden;
-            if (r < H * H) { S.wh[l][r / H][r % H] = val; S.wt[l][r % H][r / H] = val; }
-            else S.b[l + 1][r - H * H] = val;
-        } else if (i < OB4) S.w4[i - OW4] = val;
-        else S.b4[0] = val;
+// The 2x2 weight-gradient tile of compute thread t: two dz rows x two operand rows, and the
+// flat parameter index of each of the four sums (-1: padding, nothing to store).
+struct Tile {
+    int rd[2], ra[2], out[2][2];
+};
+
+__device__ __forceinline__ Tile tile_of_thread(int t) {
+    Tile T;
+    T.rd[0] = T.rd[1] = R_ZERO; T.ra[0] = T.ra[1] = R_ZERO;
+    T.out[0][0] = T.out[0][1] = T.out[1][0] = T.out[1][1] = -1;
+    if (t < 3 * kTilesHidden) {                       // hidden layer L+1: weights [j][k], bias [j]
+        const int L = t / kTilesHidden, r = t - L * kTilesHidden, jp = r / 6, kp = r - jp * 6;
+        const int base = OW1 + L * kHidden;
+#pragma unroll
+        for (int jj = 0; jj < 2; ++jj) {
+            const int j = 2 * jp + jj;
+            T.rd[jj] = R_DZ + (L + 1) * HP + j;
+            if (kp < 5) {
+                T.out[jj][0] = base + j * H + 2 * kp;
+                T.out[jj][1] = base + j * H + 2 * kp + 1;
+            } else {
+                T.out[jj][0] = base + H * H + j;      // bias: operand row of ones
+            }
+        }
+        if (kp < 5) { T.ra[0] = R_ACT + L * HP + 2 * kp; T.ra[1] = T.ra[0] + 1; }
+        else T.ra[0] = R_ONE;
+    } else if (t < 3 * kTilesHidden + kTilesL0) {     // layer 0: inputs x0, x1 and the bias
+        const int r = t - 3 * kTilesHidden, jp = r >> 1, kp = r & 1;
+#pragma unroll
+        for (int jj = 0; jj < 2; ++jj) {
+            const int j = 2 * jp + jj;
+            T.rd[jj] = R_DZ + j;
+            if (kp == 0) { T.out[jj][0] = 2 * j; T.out[jj][1] = 2 * j + 1; }
+            else T.out[jj][0] = OB0 + j;
+        }
+        if (kp == 0) { T.ra[0] = R_IN; T.ra[1] = R_IN + 1; }
+        else T.ra[0] = R_ONE;
+    } else if (t < kTiles) {                          // layer 4: one output neuron
+        const int kp = t - 3 * kTilesHidden - kTilesL0;
+        T.rd[0] = R_DZ + 4 * HP;
+        if (kp < 5) {
+            T.ra[0] = R_ACT + 3 * HP + 2 * kp; T.ra[1] = T.ra[0] + 1;
+            T.out[0][0] = OW4 + 2 * kp; T.out[0][1] = OW4 + 2 * kp + 1;
+        } else {
+            T.ra[0] = R_ONE;
+            T.out[0][0] = OB4;
+        }
     }
-    if (tid < kRowStride) S.table[R_ONE][tid] = 1.f;
+    return T;
 }
 
 __global__ void __cluster_dims__(kCluster, 1, 1) __launch_bounds__(kThreads, 1)
@@ -160,9 +229,14 @@ toy_step_kernel(const __grid_constant__ JobList jl) {
     const int B = job.B, mode = job.mode;
     const bool compute = tid < kComputeThreads;
     DDPB_STAMP(0);
-    const long long seq = job.state ? job.state->seq : 0;
 
-    // ---- optimizer warps: everything they need from HBM is requested before anything else
+    // ---- 0. every global load this kernel needs is issued before anything waits on one
+    const float *__restrict__ prm = job.params;
+    const float pv0 = prm[tid];                                   // 371 parameters over 192 threads
+    const float pv1 = (tid + kThreads < P) ? prm[tid + kThreads] : 0.f;
+    const bool need_seq = mode != DDPB_MODE_FWD && (job.loss_ring_n > 1 || (job.idx && job.idx_rows > 1));
+    const long long seq = (job.state && need_seq) ? job.state->seq : 0;
+
     const int own = cta * kSlice + (tid - kComputeThreads);     // index into the 372-entry slice table
     const bool owner = !compute && (tid - kComputeThreads) < kSlice && own <= P;
     float p_old = 0.f, m_old = 0.f, v_old = 0.f;
@@ -171,7 +245,7 @@ toy_step_kernel(const __grid_constant__ JobList jl) {
     if (mode == DDPB_MODE_STEP && !compute) {
         step = job.state->step;
         if (owner && own < P) {
-            p_old = job.params[own];
+            p_old = prm[own];
             m_old = job.m[own];
             if (job.opt == DDPB_OPT_ADAM) {
                 v_old = job.v[own];
@@ -180,9 +254,8 @@ toy_step_kernel(const __grid_constant__ JobList jl) {
             }
         }
     }
-
-    // ---- compute warps: the first batch rows are requested before the weights are staged
-    const int32_t *idx_row = job.idx ? job.idx + (long long)wrap_index(seq, job.idx_rows) * job.idx_stride : nullptr;
+    const int32_t *idx_row = nullptr;
+    if (job.idx) idx_row = job.idx + (job.idx_rows > 1 ? (long long)wrap_index(seq, job.idx_rows) * job.idx_stride : 0);
     float x0 = 0.f, x1 = 0.f, y = 0.f;
     auto fetch_sample = [&](int chunk0) {
         const int b = chunk0 + cta * kLanes + lane;
@@ -195,19 +268,32 @@ toy_step_kernel(const __grid_constant__ JobList jl) {
         }
     };
     fetch_sample(0);
-    stage_weights(S, job.params, tid);
-    __syncthreads();
+
+    // ---- 1. stage the weights: zero the padded arrays while the loads fly, then scatter
+    {
+        float *flat = reinterpret_cast<float *>(&S);
+        for (int i = tid; i < kWeightFloats; i += kThreads) flat[i] = 0.f;
+        if (tid < kRowStride) { S.table[R_ONE][tid] = 1.f; S.table[R_ZERO][tid] = 0.f; }
+        if (tid == kComputeThreads && mode != DDPB_MODE_FWD) mbar_init(&S.mbar, kCluster);
+        __syncthreads();
+        if (mode != DDPB_MODE_FWD) cluster_arrive();             // waited for just before the first remote access
+        stage_param(S, tid, pv0);
+        if (tid + kThreads < P) stage_param(S, tid + kThreads, pv1);
+        __syncthreads();
+    }
     DDPB_STAMP(1);
 
     if (!compute) {
         if (mode == DDPB_MODE_FWD) return;
         // ================= optimizer warps =================
-        cluster.sync();                                   // partials of all eight CTAs are published
+        cluster_wait();
+        mbar_wait(&S.mbar, 0);                            // all eight CTAs have pushed their partials
         DDPB_STAMP(2);
         if (owner) {
+            const int slot = tid - kComputeThreads;
             float total = 0.f;
 #pragma unroll
-            for (int c = 0; c < kCluster; ++c) total += cluster.map_shared_rank(S.partial, c)[own];
+            for (int c = 0; c < kCluster; ++c) total += S.inbox[c][slot];
             if (own == P) {
                 job.grads[P] = total;                                        // sum (o-t)^2 over the local batch
                 if (job.loss_ring) job.loss_ring[wrap_index(seq, job.loss_ring_n)] = total / (float)B;
@@ -240,72 +326,62 @@ toy_step_kernel(const __grid_constant__ JobList jl) {
             }
         }
         if (cta == 0 && tid == kComputeThreads) {          // advance the device-resident counters
-            job.state->seq = seq + 1;
+            const long long seq_now = need_seq ? seq : job.state->seq;
+            job.state->seq = seq_now + 1;
             if (mode == DDPB_MODE_STEP) job.state->step = step + 1;
         }
         DDPB_STAMP(3);
-        cluster_rendezvous_relaxed();
-        DDPB_STAMP(4);
         return;
     }
 
     // ================= compute warps =================
-    int row_dz[3], row_a[3];
-    float gacc[3] = {0.f, 0.f, 0.f};
-#pragma unroll
-    for (int r = 0; r < 3; ++r) {
-        const int i = tid + r * kComputeThreads;
-        row_dz[r] = R_ONE; row_a[r] = R_ONE;
-        if (i < P) rows_of_param(i, row_dz[r], row_a[r]);
-    }
+    const Tile T = tile_of_thread(tid);
+    float gacc[2][2] = {{0.f, 0.f}, {0.f, 0.f}};
     float sq_acc = 0.f;
     const float norm = (float)(2.0 / (double)B);        // mse_loss_backward: 2/numel
+    const int j0 = warp * kOwned;                       // first neuron owned by this warp in every layer
 
     for (int chunk0 = 0; chunk0 < B; chunk0 += kChunk) {
         const bool cta_has_samples = chunk0 + cta * kLanes < B;          // uniform per CTA
         const bool valid = chunk0 + cta * kLanes + lane < B;
         if (cta_has_samples) {
-            // neurons owned by this warp in every layer: warp, warp+4, warp+8 (the last: warps 0,1 only)
             unsigned mask[4] = {0u, 0u, 0u, 0u};          // bit i: pre-activation of owned neuron i > 0
             float cur[H];
             // ---- layer 0 (2 -> H)
             if (warp == 0) { S.table[R_IN][lane] = x0; S.table[R_IN + 1][lane] = x1; }
 #pragma unroll
             for (int i = 0; i < kOwned; ++i) {
-                const int j = warp + 4 * i;
-                if (j < H) {
-                    float acc = S.b[0][j];
-                    acc = fmaf(S.w0[j][0], x0, acc);
-                    acc = fmaf(S.w0[j][1], x1, acc);
-                    mask[0] |= (acc > 0.f ? 1u : 0u) << i;
-                    S.table[R_ACT + j][lane] = lrelu(acc);
-                }
+                const int j = j0 + i;
+                float acc = S.b[0][j];
+                acc = fmaf(S.w0[j][0], x0, acc);
+                acc = fmaf(S.w0[j][1], x1, acc);
+                mask[0] |= (acc > 0.f ? 1u : 0u) << i;
+                S.table[R_ACT + j][lane] = lrelu(acc);
             }
             compute_barrier();
-            // ---- layers 1..3 (H -> H)
+            // ---- layers 1..3 (H -> H): three interleaved 10-FMA chains per warp
 #pragma unroll
             for (int l = 0; l < 3; ++l) {
-                read_rows(S, R_ACT + l * H, lane, cur);
+                read_rows(S, R_ACT + l * HP, lane, cur);
+                float w[kOwned][HP], acc[kOwned];
+#pragma unroll
+                for (int i = 0; i < kOwned; ++i) { load_row(S.wh[l][j0 + i], w[i]); acc[i] = S.b[l + 1][j0 + i]; }
+#pragma unroll
+                for (int k = 0; k < H; ++k)
+#pragma unroll
+                    for (int i = 0; i < kOwned; ++i) acc[i] = fmaf(w[i][k], cur[k], acc[i]);
 #pragma unroll
                 for (int i = 0; i < kOwned; ++i) {
-                    const int j = warp + 4 * i;
-                    if (j < H) {
-                        float w[kWRow];
-                        load_row(S.wh[l][j], w);
-                        float acc = S.b[l + 1][j];
-#pragma unroll
-                        for (int k = 0; k < H; ++k) acc = fmaf(w[k], cur[k], acc);
-                        mask[l + 1] |= (acc > 0.f ? 1u : 0u) << i;
-                        S.table[R_ACT + (l + 1) * H + j][lane] = lrelu(acc);
-                    }
+                    mask[l + 1] |= (acc[i] > 0.f ? 1u : 0u) << i;
+                    S.table[R_ACT + (l + 1) * HP + j0 + i][lane] = lrelu(acc[i]);
                 }
                 compute_barrier();
             }
             // ---- layer 4 (H -> 1): every warp computes it, all of them need the loss gradient
             DDPB_STAMP(2);
-            read_rows(S, R_ACT + 3 * H, lane, cur);
+            read_rows(S, R_ACT + 3 * HP, lane, cur);
             float out = S.b4[0];
-            float w4[kWRow];
+            float w4[HP];
             load_row(S.w4, w4);
 #pragma unroll
             for (int k = 0; k < H; ++k) out = fmaf(w4[k], cur[k], out);
@@ -320,32 +396,27 @@ toy_step_kernel(const __grid_constant__ JobList jl) {
 #pragma unroll
                     for (int off = 16; off > 0; off >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, off);
                     sq_acc += sq;
-                    S.table[R_DZ + 4 * H][lane] = dz4;
+                    S.table[R_DZ + 4 * HP][lane] = dz4;
                 }
 #pragma unroll
                 for (int i = 0; i < kOwned; ++i) {
-                    const int k = warp + 4 * i;
-                    if (k < H) {
-                        const float g = fmaf(dz4, w4[k], 0.f);
-                        S.table[R_DZ + 3 * H + k][lane] = ((mask[3] >> i) & 1u) ? g : g * kSlope;
-                    }
+                    const float g = fmaf(dz4, S.w4[j0 + i], 0.f);            // padding neurons: weight 0
+                    S.table[R_DZ + 3 * HP + j0 + i][lane] = ((mask[3] >> i) & 1u) ? g : g * kSlope;
                 }
                 compute_barrier();
 #pragma unroll
                 for (int l = 2; l >= 0; --l) {            // through W_{l+1}: dz_{l+1} -> dz_l
-                    read_rows(S, R_DZ + (l + 1) * H, lane, cur);
+                    read_rows(S, R_DZ + (l + 1) * HP, lane, cur);
+                    float w[kOwned][HP], s[kOwned];
 #pragma unroll
-                    for (int i = 0; i < kOwned; ++i) {
-                        const int k = warp + 4 * i;
-                        if (k < H) {
-                            float w[kWRow];
-                            load_row(S.wt[l][k], w);
-                            float s = 0.f;
+                    for (int i = 0; i < kOwned; ++i) { load_row(S.wt[l][j0 + i], w[i]); s[i] = 0.f; }
 #pragma unroll
-                            for (int j = 0; j < H; ++j) s = fmaf(cur[j], w[j], s);
-                            S.table[R_DZ + l * H + k][lane] = ((mask[l] >> i) & 1u) ? s : s * kSlope;
-                        }
-                    }
+                    for (int j = 0; j < H; ++j)
+#pragma unroll
+                        for (int i = 0; i < kOwned; ++i) s[i] = fmaf(cur[j], w[i][j], s[i]);
+#pragma unroll
+                    for (int i = 0; i < kOwned; ++i)
+                        S.table[R_DZ + l * HP + j0 + i][lane] = ((mask[l] >> i) & 1u) ? s[i] : s[i] * kSlope;
                     compute_barrier();
                 }
             }
@@ -354,24 +425,27 @@ toy_step_kernel(const __grid_constant__ JobList jl) {
             if (chunk0 + kChunk < B) { compute_barrier(); fetch_sample(chunk0 + kChunk); }
             continue;
         }
-        // ---- weight gradients of this CTA's 32 samples (the table is complete: last barrier above)
+        // ---- weight gradients of this CTA's 32 samples: one 2x2 tile per thread
         DDPB_STAMP(3);
-        if (cta_has_samples) {
+        if (cta_has_samples && tid < kTiles) {
+            const float4 *d0 = reinterpret_cast<const float4 *>(S.table[T.rd[0]]);
+            const float4 *d1 = reinterpret_cast<const float4 *>(S.table[T.rd[1]]);
+            const float4 *a0 = reinterpret_cast<const float4 *>(S.table[T.ra[0]]);
+            const float4 *a1 = reinterpret_cast<const float4 *>(S.table[T.ra[1]]);
+            float s00[4] = {0.f, 0.f, 0.f, 0.f}, s01[4] = {0.f, 0.f, 0.f, 0.f};
+            float s10[4] = {0.f, 0.f, 0.f, 0.f}, s11[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-            for (int r = 0; r < 3; ++r) {
-                if (tid + r * kComputeThreads < P) {
-                    const float4 *pd = reinterpret_cast<const float4 *>(S.table[row_dz[r]]);
-                    const float4 *pa = reinterpret_cast<const float4 *>(S.table[row_a[r]]);
-                    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
-#pragma unroll
-                    for (int c = 0; c < kLanes / 4; ++c) {
-                        const float4 d = pd[c], a = pa[c];
-                        s0 = fmaf(d.x, a.x, s0); s1 = fmaf(d.y, a.y, s1);
-                        s2 = fmaf(d.z, a.z, s2); s3 = fmaf(d.w, a.w, s3);
-                    }
-                    gacc[r] += (s0 + s1) + (s2 + s3);
-                }
+            for (int c = 0; c < kLanes / 4; ++c) {
+                const float4 p = d0[c], q = d1[c], u = a0[c], v = a1[c];
+                s00[0] = fmaf(p.x, u.x, s00[0]); s00[1] = fmaf(p.y, u.y, s00[1]); s00[2] = fmaf(p.z, u.z, s00[2]); s00[3] = fmaf(p.w, u.w, s00[3]);
+                s01[0] = fmaf(p.x, v.x, s01[0]); s01[1] = fmaf(p.y, v.y, s01[1]); s01[2] = fmaf(p.z, v.z, s01[2]); s01[3] = fmaf(p.w, v.w, s01[3]);
+                s10[0] = fmaf(q.x, u.x, s10[0]); s10[1] = fmaf(q.y, u.y, s10[1]); s10[2] = fmaf(q.z, u.z, s10[2]); s10[3] = fmaf(q.w, u.w, s10[3]);
+                s11[0] = fmaf(q.x, v.x, s11[0]); s11[1] = fmaf(q.y, v.y, s11[1]); s11[2] = fmaf(q.z, v.z, s11[2]); s11[3] = fmaf(q.w, v.w, s11[3]);
             }
+            gacc[0][0] += (s00[0] + s00[1]) + (s00[2] + s00[3]);
+            gacc[0][1] += (s01[0] + s01[1]) + (s01[2] + s01[3]);
+            gacc[1][0] += (s10[0] + s10[1]) + (s10[2] + s10[3]);
+            gacc[1][1] += (s11[0] + s11[1]) + (s11[2] + s11[3]);
         }
         if (chunk0 + kChunk < B) {                         // another pass: the table is about to be overwritten
             compute_barrier();
@@ -380,16 +454,23 @@ toy_step_kernel(const __grid_constant__ JobList jl) {
     }
     if (mode == DDPB_MODE_FWD) return;
 
-    // ---- publish the partials; the optimizer warps of the cluster take it from here
-#pragma unroll
-    for (int r = 0; r < 3; ++r)
-        if (tid + r * kComputeThreads < P) S.partial[tid + r * kComputeThreads] = gacc[r];
-    if (tid == 0) S.partial[P] = sq_acc;
+    // ---- push the partials into the inbox of the CTA that owns each parameter slice
     DDPB_STAMP(4);
-    cluster.sync();
+    cluster_wait();                                       // every CTA runs and has initialised its mbarrier
+#pragma unroll
+    for (int jj = 0; jj < 2; ++jj)
+#pragma unroll
+        for (int kk = 0; kk < 2; ++kk) {
+            const int i = T.out[jj][kk];
+            if (i >= 0) {
+                const int dst = i / kSlice;
+                *cluster.map_shared_rank(&S.inbox[cta][i - dst * kSlice], dst) = gacc[jj][kk];
+            }
+        }
+    if (tid == 0) *cluster.map_shared_rank(&S.inbox[cta][P % kSlice], P / kSlice) = sq_acc;
+    compute_barrier();
+    if (tid < kCluster) mbar_arrive_remote(&S.mbar, (unsigned)tid);
     DDPB_STAMP(5);
-    cluster_rendezvous_relaxed();
-    DDPB_STAMP(6);
 }
 
 }  // namespace

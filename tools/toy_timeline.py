@@ -5,8 +5,7 @@ Builds a -DDDPB_TIMELINE variant of the library into gpurun_out/ (the product li
 touched), runs 200 fused steps of the two-model job and prints, for the last step, the cycle
 stamps of every warp of every CTA relative to the earliest stamp of its cluster.
 Compute warps 0-3: 0 start, 1 weights staged, 2 before layer 4, 3 before weight gradients,
-4 partials written, 5 after cluster.sync, 6 end.  Optimizer warps 4-5: 0 start, 1 staged,
-2 after cluster.sync, 3 update stored, 4 end.
+4 before the push, 5 end.  Optimizer warps 4-5: 0 start, 1 staged, 2 partials arrived, 3 end.
 """
 import ctypes
 import os
