@@ -4,8 +4,9 @@
 Builds a -DDDPB_TIMELINE variant of the library into gpurun_out/ (the product library is not
 touched), runs 200 fused steps of the two-model job and prints, for the last step, the cycle
 stamps of every warp of every CTA relative to the earliest stamp of its cluster.
-Compute warps 0-3: 0 start, 1 weights staged, 2 before layer 4, 3 before weight gradients,
-4 before the push, 5 end.  Optimizer warps 4-5: 0 start, 1 staged, 2 partials arrived, 3 end.
+Compute warps 0-3: 0 start, 1 smem zeroed, 2 weights staged, 3 layer 0 done (inputs arrived),
+4 before layer 4, 5 before weight gradients, 6 before the push, 7 end.
+Optimizer warps 4-5: 0 start, 1 smem zeroed, 2 staged, 3 partials arrived, 4 end.
 """
 import ctypes
 import os
@@ -56,6 +57,6 @@ for model in range(2):
     print(f"model {model}: cycles relative to the cluster's first stamp")
     for cta in (0, 3, 7):
         for warp in range(6):
-            rel = [int(v - base) if v > 0 else -1 for v in t[model, cta, warp, :7]]
+            rel = [int(v - base) if v > 0 else -1 for v in t[model, cta, warp, :8]]
             print(f"  cta {cta} warp {warp}: {rel}")
 print("loss", float(keep[0]["r"][199]), float(keep[1]["r"][199]))
