@@ -267,7 +267,7 @@ def ours(args):
         for i, m in enumerate((model_X, model_Y)):
             j = m._backend.job
             j.x, j.y, j.idx = loader._dev[0].data_ptr(), loader._dev[1].data_ptr(), rows.data_ptr()
-            j.idx_rows, j.idx_stride, j.B, j.mode = n_rows, BATCH, BATCH, _lib.MODE_STEP
+            j.idx_rows, j.idx_stride, j.B, j.mode, j.n_data = n_rows, BATCH, BATCH, _lib.MODE_STEP, DATASET
             jobs[i] = j
         stream = torch.cuda.current_stream().cuda_stream
         toy_step = _lib.lib().ddpb_toy_step
@@ -283,7 +283,9 @@ def ours(args):
                 _lib.check(toy_step(jobs, 2, cap), "ddpb_toy_step")
             side_stream.synchronize()
             _lib.check(L.ddpb_graph_begin(cap), "ddpb_graph_begin")
-            for _ in range(K):
+            for i in range(K):
+                for k in range(2):           # every graph node carries its own sampler row: no device-side lookup
+                    jobs[k].idx, jobs[k].idx_rows = rows.data_ptr() + (i % n_rows) * BATCH * 4, 1
                 _lib.check(toy_step(jobs, 2, cap), "ddpb_toy_step")
             _lib.check(L.ddpb_graph_end(cap, ctypes.byref(graph)), "ddpb_graph_end")
             _lib.check(L.ddpb_graph_launch(graph, cap), "ddpb_graph_launch")      # warm the instantiated graph

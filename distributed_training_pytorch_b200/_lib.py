@@ -30,7 +30,7 @@ class ToyJob(ctypes.Structure):
                 ("state", c_void_p), ("bias_table", c_void_p), ("loss_ring", c_void_p), ("x", c_void_p), ("y", c_void_p),
                 ("idx", c_void_p), ("out", c_void_p),
                 ("B", c_int32), ("mode", c_int32), ("opt", c_int32), ("loss_ring_n", c_int32),
-                ("idx_rows", c_int32), ("idx_stride", c_int32), ("bias_table_n", c_int32), ("reserved", c_int32),
+                ("idx_rows", c_int32), ("idx_stride", c_int32), ("bias_table_n", c_int32), ("n_data", c_int32),
                 ("lr", c_double), ("beta1", c_double), ("beta2", c_double), ("eps", c_double),
                 ("momentum", c_double)]
 

@@ -69,6 +69,9 @@ constexpr int R_DZ = R_ZERO + 1;                 // dz_0 .. dz_3, then dz_4
 constexpr int kRows = R_DZ + 4 * HP + 1;
 constexpr int kSlice = (P + 1 + kCluster - 1) / kCluster;   // 47 values per CTA (371 grads + loss sum)
 constexpr int kInboxRow = 48;
+constexpr int kMaxStagedRows = 1024;             // datasets up to this many rows are staged in shared memory
+constexpr int kStageX = (2 * kMaxStagedRows / 4 + kThreads - 1) / kThreads;   // float4 loads per thread
+constexpr int kStageY = (kMaxStagedRows / 4 + kThreads - 1) / kThreads;
 static_assert(kSlice <= kThreads - kComputeThreads && kSlice <= kInboxRow, "the optimizer warps must cover a slice");
 
 // weight-gradient tiles: 3 hidden layers x (5 neuron pairs x 6 input pairs) + layer 0 (5 x 2) + layer 4 (1 x 6)
@@ -88,6 +91,8 @@ struct __align__(16) Smem {
     float b[4][HP];            // biases of layers 0..3
     float b4[4];
     float table[kRows][kRowStride];
+    float data_x[2 * kMaxStagedRows];   // the whole dataset when it is small (gather without a dependent HBM trip)
+    float data_y[kMaxStagedRows];
     float inbox[kCluster][kInboxRow];   // partial sums pushed by the cluster's CTAs for MY slice
     unsigned long long mbar;            // counts the 8 "pushed" arrivals
 };
@@ -268,8 +273,28 @@ toy_step_kernel(const __grid_constant__ JobList jl) {
             }
         }
     }
+    // The batch: rows idx_row[b] of the dataset (or row b of a ready-made batch).  A dependent
+    // index -> row load costs a second ~800-cycle L2 round trip, so a small dataset is pulled
+    // into shared memory wholesale, in parallel with the index load, and gathered from there.
     const int32_t *idx_row = nullptr;
     if (job.idx) idx_row = job.idx + (job.idx_rows > 1 ? (long long)wrap_index(seq, job.idx_rows) * job.idx_stride : 0);
+    const int n_staged = (idx_row && job.n_data > 0 && job.n_data <= kMaxStagedRows && B <= kChunk) ? job.n_data : 0;
+    float4 stage_x[kStageX], stage_y[kStageY];
+    int my_row = -1;
+    if (n_staged) {
+        const int b = cta * kLanes + lane;
+        if (compute && b < B) my_row = idx_row[b];
+#pragma unroll
+        for (int r = 0; r < kStageX; ++r) {
+            const int i = tid + r * kThreads;
+            stage_x[r] = (4 * i < 2 * n_staged) ? reinterpret_cast<const float4 *>(job.x)[i] : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+#pragma unroll
+        for (int r = 0; r < kStageY; ++r) {
+            const int i = tid + r * kThreads;
+            stage_y[r] = (4 * i < n_staged && mode != DDPB_MODE_FWD) ? reinterpret_cast<const float4 *>(job.y)[i] : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+    }
     float x0 = 0.f, x1 = 0.f, y = 0.f;
     auto fetch_sample = [&](int chunk0) {
         const int b = chunk0 + cta * kLanes + lane;
@@ -281,7 +306,7 @@ toy_step_kernel(const __grid_constant__ JobList jl) {
             if (mode != DDPB_MODE_FWD) y = job.y[s];
         }
     };
-    fetch_sample(0);
+    if (!n_staged) fetch_sample(0);
 
     // ---- 1. stage the weights: zero the padded arrays while the loads fly, then scatter
     {
@@ -298,7 +323,16 @@ toy_step_kernel(const __grid_constant__ JobList jl) {
         if (mode != DDPB_MODE_FWD) cluster_arrive();             // waited for just before the first remote access
         stage_param(S, tid, pv0);
         if (tid + kThreads < P) stage_param(S, tid + kThreads, pv1);
+        if (n_staged) {
+#pragma unroll
+            for (int r = 0; r < kStageX; ++r)
+                if (4 * (tid + r * kThreads) < 2 * n_staged) reinterpret_cast<float4 *>(S.data_x)[tid + r * kThreads] = stage_x[r];
+#pragma unroll
+            for (int r = 0; r < kStageY; ++r)
+                if (4 * (tid + r * kThreads) < n_staged) reinterpret_cast<float4 *>(S.data_y)[tid + r * kThreads] = stage_y[r];
+        }
         __syncthreads();
+        if (n_staged && my_row >= 0) { x0 = S.data_x[2 * my_row]; x1 = S.data_x[2 * my_row + 1]; y = S.data_y[my_row]; }
     }
     DDPB_STAMP(2);
 
@@ -306,6 +340,14 @@ toy_step_kernel(const __grid_constant__ JobList jl) {
         if (mode == DDPB_MODE_FWD) return;
         // ================= optimizer warps =================
         cluster_wait();
+        // everything that does not depend on the gradients is in registers before the wait
+        const float w1 = (float)(1.0 - job.beta1), b2 = (float)job.beta2;
+        const float w2 = (float)(1.0 - job.beta2), eps = (float)job.eps;
+        const float lr_f = (float)job.lr, mo = (float)job.momentum;
+        const int opt = job.opt;
+        float *const g_out = job.grads, *const p_out = job.params, *const m_out = job.m, *const v_out = job.v;
+        float *const loss_slot = job.loss_ring ? job.loss_ring + wrap_index(seq, job.loss_ring_n) : nullptr;
+        const float inv_B = __fdiv_rn(1.0f, (float)B);
         mbar_wait(&S.mbar, 0);                            // all eight CTAs have pushed their partials
         DDPB_STAMP(3);
         if (owner) {
@@ -314,32 +356,29 @@ toy_step_kernel(const __grid_constant__ JobList jl) {
 #pragma unroll
             for (int c = 0; c < kCluster; ++c) total += S.inbox[c][slot];
             if (own == P) {
-                job.grads[P] = total;                                        // sum (o-t)^2 over the local batch
-                if (job.loss_ring) job.loss_ring[wrap_index(seq, job.loss_ring_n)] = total / (float)B;
+                g_out[P] = total;                                            // sum (o-t)^2 over the local batch
+                if (loss_slot) *loss_slot = (B & (B - 1)) == 0 ? total * inv_B : __fdiv_rn(total, (float)B);
             } else {
-                job.grads[own] = total;
+                g_out[own] = total;
                 if (mode == DDPB_MODE_STEP) {
                     const float g = total;
-                    if (job.opt == DDPB_OPT_ADAM) {
+                    if (opt == DDPB_OPT_ADAM) {
                         // torch:optim/adam.py:457 (lerp), :476 (mul, addcmul), :545 (denom), :547 (addcdiv);
                         // bias.x = -(lr / (1 - beta1^t)), bias.y = sqrt(1 - beta2^t): host table (:531-536)
-                        const float w1 = (float)(1.0 - job.beta1), b2 = (float)job.beta2;
-                        const float w2 = (float)(1.0 - job.beta2), eps = (float)job.eps;
                         const float m_new = __fmaf_rn(w1, __fsub_rn(g, m_old), m_old);
                         const float v_new = __fadd_rn(__fmul_rn(v_old, b2), __fmul_rn(__fmul_rn(w2, g), g));
                         const float denom = __fadd_rn(__fdiv_rn(__fsqrt_rn(v_new), bias.y), eps);
-                        job.params[own] = __fadd_rn(p_old, __fmul_rn(bias.x, __fdiv_rn(m_new, denom)));
-                        job.m[own] = m_new;
-                        job.v[own] = v_new;
+                        p_out[own] = __fadd_rn(p_old, __fmul_rn(bias.x, __fdiv_rn(m_new, denom)));
+                        m_out[own] = m_new;
+                        v_out[own] = v_new;
                     } else {
                         // torch:optim/sgd.py _single_tensor_sgd: buf = g (first step) | momentum*buf + g
                         float d = g;
-                        if (job.momentum != 0.0) {
-                            const float mo = (float)job.momentum;
+                        if (mo != 0.f) {
                             d = (step == 0) ? g : __fadd_rn(__fmul_rn(m_old, mo), g);
-                            job.m[own] = d;
+                            m_out[own] = d;
                         }
-                        job.params[own] = __fsub_rn(p_old, __fmul_rn((float)job.lr, d));
+                        p_out[own] = __fsub_rn(p_old, __fmul_rn(lr_f, d));
                     }
                 }
             }
@@ -513,6 +552,8 @@ DDPB_API int ddpb_toy_step(const ddpb_toy_job *jobs, int njobs, void *stream) {
         if (q.loss_ring) DDPB_REQUIRE(q.loss_ring_n >= 1, "ddpb_toy_step: job %d: empty loss ring", j);
         if (q.idx) DDPB_REQUIRE(q.idx_rows >= 1 && q.idx_stride >= q.B, "ddpb_toy_step: job %d: index rows too short", j);
         jl.jobs[j] = q;
+        // the shared-memory staging of a small dataset needs whole, aligned float4 rows
+        if (!q.idx || q.n_data < 0 || (q.n_data & 3) || ((uintptr_t)q.x & 15) || ((uintptr_t)q.y & 15)) jl.jobs[j].n_data = 0;
     }
     toy_step_kernel<<<dim3(kCluster, njobs, 1), kThreads, 0, (cudaStream_t)stream>>>(jl);
     DDPB_CUDA(cudaGetLastError());

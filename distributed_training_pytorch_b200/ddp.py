@@ -200,13 +200,13 @@ class ToyBackend:
             target = target.cuda(self.device)
         if isinstance(data, DeviceBatch):
             j.x, j.y, j.idx, j.B = data.x.data_ptr(), data.y.data_ptr(), data.idx_ptr, data.B
-            j.idx_stride = data.B
+            j.idx_stride, j.n_data = data.B, data.x.shape[0]
             self.keep = [data.keep]
             return
         if not (isinstance(data, torch.Tensor) and data.is_cuda and data.dtype == torch.float32
                 and data.dim() == 2 and data.shape[1] == 2 and data.is_contiguous()):
             raise _lib.DdpB200Error("model input must be a contiguous float32 CUDA tensor [B,2] (or a loader batch)")
-        j.x, j.idx, j.B, j.idx_stride = data.data_ptr(), None, data.shape[0], 0
+        j.x, j.idx, j.B, j.idx_stride, j.n_data = data.data_ptr(), None, data.shape[0], 0, 0
         self.keep = [data]
         if target is not None:
             if isinstance(target, DeviceBatch):

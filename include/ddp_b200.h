@@ -104,7 +104,8 @@ typedef struct ddpb_toy_job {
     int32_t opt;              /* DDPB_OPT_* */
     int32_t loss_ring_n;
     int32_t idx_rows, idx_stride;
-    int32_t bias_table_n, reserved;
+    int32_t bias_table_n;
+    int32_t n_data;           /* rows of the dataset behind idx (0 = unknown): <= 1024 rows are staged on chip */
     double lr, beta1, beta2, eps, momentum;
 } ddpb_toy_job;
 

@@ -47,12 +47,13 @@ class ToyHarness:
         self.seq = 0
         self.keep = None
 
-    def bind(self, x, y, mode, idx=None, idx_rows=1, idx_stride=0, B=None, out=None):
+    def bind(self, x, y, mode, idx=None, idx_rows=1, idx_stride=0, B=None, out=None, staged=True):
         j = self.job
         self.keep = (x, y, idx, out)
         j.x, j.y = x.data_ptr(), (y.data_ptr() if y is not None else None)
         j.idx = idx.data_ptr() if idx is not None else None
         j.idx_rows, j.idx_stride = idx_rows, idx_stride
+        j.n_data = x.shape[0] if (idx is not None and staged) else 0
         j.B = int(B if B is not None else x.shape[0])
         j.mode = mode
         j.out = out.data_ptr() if out is not None else None

@@ -64,13 +64,15 @@ def test_gathered_batch_equals_direct_batch(oracle, native_lib, golden_dir):
     g = np.load(os.path.join(golden_dir, "ref_w1.npz"))
     rows = np.stack([oracle.sampler_indices(512, 2, 1, epoch=e) for e in range(3)]).astype(np.int32)
     X, Y, idx = dev(d["x"]), dev(d["y"]), dev(rows, torch.int32)
-    a, b = ToyHarness(g["init_X"]), ToyHarness(g["init_X"])
+    a, b, c = ToyHarness(g["init_X"]), ToyHarness(g["init_X"]), ToyHarness(g["init_X"])
     for e in range(3):
-        a.bind(X, Y, _lib.MODE_GRAD, idx=idx, idx_rows=3, idx_stride=256, B=256)     # row picked by seq % 3
+        a.bind(X, Y, _lib.MODE_GRAD, idx=idx, idx_rows=3, idx_stride=256, B=256)     # row picked by seq % 3; dataset staged on chip
         a.launch()
         b.bind(dev(d["x"][rows[e]]), dev(d["y"][rows[e]]), _lib.MODE_GRAD)
         b.launch()
-        assert torch.equal(a.grads, b.grads), e
+        c.bind(X, Y, _lib.MODE_GRAD, idx=idx, idx_rows=3, idx_stride=256, B=256, staged=False)   # dependent-load gather
+        c.launch()
+        assert torch.equal(a.grads, b.grads) and torch.equal(c.grads, b.grads), e
 
 
 @pytest.mark.parametrize("opt,momentum", [(_lib.OPT_ADAM, 0.0), (_lib.OPT_SGD, 0.0), (_lib.OPT_SGD, 0.9)])

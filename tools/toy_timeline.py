@@ -43,7 +43,8 @@ for i, key in enumerate(("init_X", "init_Y")):
     j.params, j.grads, j.m, j.v, j.state = (bufs[k].data_ptr() for k in "pgmvs")
     j.loss_ring, j.loss_ring_n = bufs["r"].data_ptr(), 1024
     j.bias_table, j.bias_table_n = table.data_ptr(), table.shape[0]
-    j.x, j.y, j.idx, j.idx_rows, j.idx_stride = X.data_ptr(), Y.data_ptr(), rows.data_ptr(), 64, 256
+    j.x, j.y, j.idx, j.idx_rows, j.idx_stride = X.data_ptr(), Y.data_ptr(), rows.data_ptr(), int(os.environ.get('ROWS', 1)), 256
+    j.n_data = int(os.environ.get('NDATA', 512))
     j.B, j.mode, j.opt = int(os.environ.get("B", 256)), _lib.MODE_STEP, _lib.OPT_ADAM
     j.lr, j.beta1, j.beta2, j.eps = 1e-3, 0.9, 0.999, 1e-8
     j.out = stamps.data_ptr()
