@@ -204,14 +204,14 @@ __device__ __forceinline__ Tile tile_of_thread(int t) {
         for (int jj = 0; jj < 2; ++jj) {
             const int j = 2 * jp + jj;
             T.rd[jj] = R_DZ + (L + 1) * HP + j;
-            if (kp < 5) {
-                T.out[jj][0] = base + j * H + 2 * kp;
-                T.out[jj][1] = base + j * H + 2 * kp + 1;
+            if (kp < 5) {                             // inputs k and k+5: consecutive threads read
+                T.out[jj][0] = base + j * H + kp;     // consecutive table rows (no bank conflicts)
+                T.out[jj][1] = base + j * H + kp + 5;
             } else {
                 T.out[jj][0] = base + H * H + j;      // bias: operand row of ones
             }
         }
-        if (kp < 5) { T.ra[0] = R_ACT + L * HP + 2 * kp; T.ra[1] = T.ra[0] + 1; }
+        if (kp < 5) { T.ra[0] = R_ACT + L * HP + kp; T.ra[1] = T.ra[0] + 5; }
         else T.ra[0] = R_ONE;
     } else if (t < 3 * kTilesHidden + kTilesL0) {     // layer 0: inputs x0, x1 and the bias
         const int r = t - 3 * kTilesHidden, jp = r >> 1, kp = r & 1;
@@ -228,8 +228,8 @@ __device__ __forceinline__ Tile tile_of_thread(int t) {
         const int kp = t - 3 * kTilesHidden - kTilesL0;
         T.rd[0] = R_DZ + 4 * HP;
         if (kp < 5) {
-            T.ra[0] = R_ACT + 3 * HP + 2 * kp; T.ra[1] = T.ra[0] + 1;
-            T.out[0][0] = OW4 + 2 * kp; T.out[0][1] = OW4 + 2 * kp + 1;
+            T.ra[0] = R_ACT + 3 * HP + kp; T.ra[1] = T.ra[0] + 5;
+            T.out[0][0] = OW4 + kp; T.out[0][1] = OW4 + kp + 5;
         } else {
             T.ra[0] = R_ONE;
             T.out[0][0] = OB4;
@@ -306,6 +306,7 @@ toy_step_kernel(const __grid_constant__ JobList jl) {
         }
     };
     if (!n_staged) fetch_sample(0);
+    const Tile T = tile_of_thread(tid);                // integer work, done while the loads fly
 
     // ---- 1. stage the weights: zero the padded arrays while the loads fly, then scatter
     {
@@ -398,7 +399,6 @@ toy_step_kernel(const __grid_constant__ JobList jl) {
     }
 
     // ================= compute warps =================
-    const Tile T = tile_of_thread(tid);
     float gacc[2][2] = {{0.f, 0.f}, {0.f, 0.f}};
     float sq_acc = 0.f;
     const float norm = __fdiv_rn(2.0f, (float)B);       // mse_loss_backward: 2/numel (== (float)(2.0/B) for B < 2^24)
@@ -456,10 +456,7 @@ toy_step_kernel(const __grid_constant__ JobList jl) {
                 const float diff = valid ? out - y : 0.f;
                 const float dz4 = norm * diff;
                 if (warp == 0) {
-                    float sq = diff * diff;
-#pragma unroll
-                    for (int off = 16; off > 0; off >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, off);
-                    sq_acc += sq;
+                    sq_acc = fmaf(diff, diff, sq_acc);                       // per lane; reduced once, after the loop
                     S.table[R_DZ + 4 * HP][lane] = dz4;
                 }
 #pragma unroll
@@ -531,13 +528,17 @@ toy_step_kernel(const __grid_constant__ JobList jl) {
                 push_f32(&S.inbox[cta][i - dst * kSlice], &S.mbar, (unsigned)dst, gacc[jj][kk]);
             }
         }
-    if (tid == 0) push_f32(&S.inbox[cta][P % kSlice], &S.mbar, (unsigned)(P / kSlice), sq_acc);
+    if (warp == 0) {
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) sq_acc += __shfl_xor_sync(0xffffffffu, sq_acc, off);
+        if (lane == 0) push_f32(&S.inbox[cta][P % kSlice], &S.mbar, (unsigned)(P / kSlice), sq_acc);
+    }
     DDPB_STAMP(7);
 }
 
 }  // namespace
 
-DDPB_API int ddpb_toy_step(const ddpb_toy_job *jobs, int njobs, void *stream) {
+static int launch_toy_step(const ddpb_toy_job *jobs, int njobs, cudaStream_t stream) {
     DDPB_REQUIRE(jobs != nullptr && njobs >= 1 && njobs <= DDPB_MAX_JOBS,
                  "ddpb_toy_step: njobs must be 1..%d, got %d", DDPB_MAX_JOBS, njobs);
     JobList jl;
@@ -560,7 +561,20 @@ DDPB_API int ddpb_toy_step(const ddpb_toy_job *jobs, int njobs, void *stream) {
         // the shared-memory staging of a small dataset needs whole, aligned float4 rows
         if (!q.idx || q.n_data < 0 || (q.n_data & 3) || ((uintptr_t)q.x & 15) || ((uintptr_t)q.y & 15)) jl.jobs[j].n_data = 0;
     }
-    toy_step_kernel<<<dim3(kCluster, njobs, 1), kThreads, 0, (cudaStream_t)stream>>>(jl);
+    toy_step_kernel<<<dim3(kCluster, njobs, 1), kThreads, 0, stream>>>(jl);
     DDPB_CUDA(cudaGetLastError());
     return 0;
+}
+
+DDPB_API int ddpb_toy_step(const ddpb_toy_job *jobs, int njobs, void *stream) {
+    return launch_toy_step(jobs, njobs, (cudaStream_t)stream);
+}
+
+DDPB_API int ddpb_toy_step_h2d(const ddpb_toy_job *jobs, int njobs, void *dst_dev, const void *src_host,
+                               int64_t bytes, void *stream) {
+    if (bytes > 0) {
+        DDPB_REQUIRE(dst_dev && src_host, "ddpb_toy_step_h2d: null copy operand");
+        DDPB_CUDA(cudaMemcpyAsync(dst_dev, src_host, (size_t)bytes, cudaMemcpyHostToDevice, (cudaStream_t)stream));
+    }
+    return launch_toy_step(jobs, njobs, (cudaStream_t)stream);
 }

@@ -79,3 +79,36 @@ DDPB_API int ddpb_graph_destroy(void *graph_exec) {
     if (graph_exec) DDPB_CUDA(cudaGraphExecDestroy((cudaGraphExec_t)graph_exec));
     return 0;
 }
+
+// ---- waiting for a result the kernel writes straight into pinned host memory
+// The reference blocks on loss.detach().cpu() every iteration (demo.py:115,117): a D2H copy
+// plus a stream synchronisation, ~10 us of driver latency for 4 bytes.  Here the kernel stores
+// the loss into a pinned, device-mapped ring; the host pre-fills the slot with a sentinel and
+// polls it.  A slot that still holds the sentinel after `spin_ns` (a NaN loss, an error) falls
+// back to cudaStreamSynchronize so failures surface as CUDA errors, not as hangs.
+#include <chrono>
+
+DDPB_API int ddpb_wait_f32(const float *host_slot, uint32_t sentinel_bits, int64_t spin_ns, void *stream, float *out) {
+    DDPB_REQUIRE(host_slot && out, "ddpb_wait_f32: null argument");
+    const volatile uint32_t *slot = reinterpret_cast<const volatile uint32_t *>(host_slot);
+    uint32_t bits = *slot;
+    if (bits == sentinel_bits) {
+        const auto t0 = std::chrono::steady_clock::now();
+        int spins = 0;
+        while ((bits = *slot) == sentinel_bits) {
+            if ((++spins & 63) == 0 &&
+                std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::steady_clock::now() - t0).count() > spin_ns) {
+                DDPB_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+                bits = *slot;
+                break;
+            }
+#if defined(__x86_64__)
+            __builtin_ia32_pause();
+#endif
+        }
+    }
+    union { uint32_t u; float f; } cvt;
+    cvt.u = bits;
+    *out = cvt.f;
+    return 0;
+}

@@ -73,39 +73,75 @@ class HostBatch:
     """One half (data or target) of a staged batch in pinned host memory.
 
     Quacks like the pinned tensor the reference's DataLoader yields: .cuda()/.to(device)
-    move it (one async copy for the whole (x, y) block on first use), .size()/.shape
-    describe it; any other attribute is looked up on the pinned tensor itself."""
+    hand back the device twin (one async H2D copy of the whole (x, y) block, issued together
+    with the step that consumes it), .size()/.shape describe it; any other attribute is
+    looked up on the pinned tensor itself."""
 
-    __slots__ = ("_stage", "_which")
+    __slots__ = ("stage", "which")
 
     def __init__(self, stage, which):
-        self._stage, self._which = stage, which
+        self.stage, self.which = stage, which
 
     @property
     def tensor(self):
-        return self._stage.host[self._which]
+        return self.stage.host[self.which]
 
     def cuda(self, device=None, non_blocking=False):
-        return self._stage.to_device(device)[self._which]
+        return self.stage.staged(device)[self.which]
 
     def to(self, device=None, *args, **kwargs):
         dev = torch.device(device) if device is not None and not isinstance(device, torch.dtype) else None
         if dev is None or dev.type == "cpu":
             return self.tensor
-        return self._stage.to_device(dev)[self._which]
+        return self.stage.staged(dev)[self.which]
 
     def size(self, dim=None):
-        return self.tensor.size() if dim is None else self.tensor.size(dim)
+        return self.stage.host[self.which].size() if dim is None else self.stage.host[self.which].size(dim)
 
     @property
     def shape(self):
-        return self.tensor.shape
+        return self.stage.host[self.which].shape
 
     def __len__(self):
-        return self.tensor.shape[0]
+        return self.stage.B
 
     def __getattr__(self, name):
-        return getattr(self._stage.host[self._which], name)
+        return getattr(self.stage.host[self.which], name)
+
+
+class StagedBatch:
+    """Device twin of a HostBatch.  The copy is deferred until the step that reads the batch
+    is launched (one host call does both); touching it as a tensor (`.tensor()` or any tensor
+    attribute) performs the copy immediately."""
+
+    __slots__ = ("stage", "which")
+
+    def __init__(self, stage, which):
+        self.stage, self.which = stage, which
+
+    def tensor(self):
+        self.stage.copy_now()
+        return self.stage.dev[self.which]
+
+    def cuda(self, device=None, non_blocking=False):
+        return self
+
+    def to(self, *args, **kwargs):
+        return self
+
+    def size(self, dim=None):
+        shape = self.stage.host[self.which].shape
+        return shape if dim is None else shape[dim]
+
+    @property
+    def shape(self):
+        return self.stage.host[self.which].shape
+
+    def __len__(self):
+        return self.stage.B
+
+    def __getattr__(self, name):
+        return getattr(self.tensor(), name)
 
 
 class _Stage:
@@ -114,43 +150,58 @@ class _Stage:
     def __init__(self, batch, dx, dy):
         self.block = torch.empty(batch * (dx + dy), dtype=torch.float32, pin_memory=torch.cuda.is_available())
         self.batch, self.dx, self.dy = batch, dx, dy
-        self._dev = {}         # device index -> (block, views by B)
-        self._copied_to = None
+        self.nbytes = self.block.numel() * 4
+        self.host_ptr = self.block.data_ptr()
+        self.host_x_ptr, self.host_y_ptr = self.host_ptr, self.host_ptr + batch * dx * 4
+        self._host_views, self._dev_views = {}, {}
+        self.device = None          # device index of the twin
+        self.dblock = None
+        self.dev_x_ptr = self.dev_y_ptr = 0
+        self.copied = True          # nothing to copy yet
+        self.halves = (HostBatch(self, 0), HostBatch(self, 1))
+        self.twins = (StagedBatch(self, 0), StagedBatch(self, 1))
         self.set_rows(batch)
 
     def set_rows(self, B):
         self.B = B
-        self.host = (self.block[:B * self.dx].view(B, self.dx),
+        views = self._host_views.get(B)
+        if views is None:
+            views = (self.block[:B * self.dx].view(B, self.dx),
                      self.block[self.batch * self.dx:self.batch * self.dx + B * self.dy].view(B, self.dy))
-        self._copied_to = None
+            self._host_views[B] = views
+        self.host = views
+        self.copied = False
+        if self.dblock is not None:
+            self.dev = self._device_views(B)
 
-    def to_device(self, device=None):
-        idx = torch.cuda.current_device() if device is None else torch.device(device).index
-        if idx is None:
-            idx = torch.cuda.current_device()
-        if self._copied_to is not None and self._copied_to[0] == idx:
-            return self._copied_to[1]
-        entry = self._dev.get(idx)
-        if entry is None:
-            entry = (torch.empty_like(self.block, device=f"cuda:{idx}"), {})
-            self._dev[idx] = entry
-        dblock, views = entry
-        pair = views.get(self.B)
-        if pair is None:
-            pair = (dblock[:self.B * self.dx].view(self.B, self.dx),
-                    dblock[self.batch * self.dx:self.batch * self.dx + self.B * self.dy].view(self.B, self.dy))
-            views[self.B] = pair
-        with torch.cuda.device(idx):
-            stream = torch.cuda.current_stream().cuda_stream
-            nbytes = self.block.numel() * 4 if self.B == self.batch else None
-            L = _lib.lib()
-            if nbytes is not None:      # full batch: x and y are adjacent, one copy
-                _lib.check(L.ddpb_memcpy_h2d_async(dblock.data_ptr(), self.block.data_ptr(), nbytes, stream), "h2d")
-            else:
-                _lib.check(L.ddpb_memcpy_h2d_async(pair[0].data_ptr(), self.host[0].data_ptr(), self.B * self.dx * 4, stream), "h2d")
-                _lib.check(L.ddpb_memcpy_h2d_async(pair[1].data_ptr(), self.host[1].data_ptr(), self.B * self.dy * 4, stream), "h2d")
-        self._copied_to = (idx, pair)
-        return pair
+    def _device_views(self, B):
+        views = self._dev_views.get(B)
+        if views is None:
+            views = (self.dblock[:B * self.dx].view(B, self.dx),
+                     self.dblock[self.batch * self.dx:self.batch * self.dx + B * self.dy].view(B, self.dy))
+            self._dev_views[B] = views
+        return views
+
+    def staged(self, device=None):
+        if self.dblock is None or (device is not None and torch.device(device).index not in (None, self.device)):
+            idx = torch.cuda.current_device() if device is None else torch.device(device).index
+            idx = torch.cuda.current_device() if idx is None else idx
+            self.device = idx
+            self.dblock = torch.empty_like(self.block, device=f"cuda:{idx}")
+            self.dev_x_ptr = self.dblock.data_ptr()
+            self.dev_y_ptr = self.dev_x_ptr + self.batch * self.dx * 4
+            self._dev_views = {}
+            self.dev = self._device_views(self.B)
+        return self.twins
+
+    def copy_now(self):
+        """Issue the H2D copy on the current stream unless a step launch already carried it."""
+        if not self.copied:
+            from .engine import engine_for
+            eng = engine_for(self.device)
+            eng.drop_pending_copy(self)
+            _lib.check(eng.lib.ddpb_memcpy_h2d_async(self.dev_x_ptr, self.host_ptr, self.nbytes, eng.stream()), "h2d")
+            self.copied = True
 
 
 class DeviceBatch:
@@ -195,7 +246,7 @@ class DataLoader:
     there is nothing for worker processes to do.  shuffle=True without a sampler is not
     used by the reference and is rejected rather than approximated."""
 
-    STAGES = 4
+    STAGES = 8
     EPOCH_ROWS = 256        # index rows uploaded at a time on the device-resident path
 
     def __init__(self, dataset, batch_size=1, shuffle=False, sampler=None, pin_memory=False, num_workers=0,
@@ -233,7 +284,7 @@ class DataLoader:
             self._stages = [_Stage(self.batch_size, self.dx, self.dy) for _ in range(self.STAGES)]
         idx = self._indices()
         L = _lib.lib()
-        xp, yp = self.x.data_ptr(), self.y.data_ptr()
+        xp, yp, idx_ptr = self.x.data_ptr(), self.y.data_ptr(), idx.ctypes.data
         for start in range(0, len(idx), self.batch_size):
             B = min(self.batch_size, len(idx) - start)
             if B < self.batch_size and self.drop_last:
@@ -241,9 +292,10 @@ class DataLoader:
             stage = self._stages[self._next_stage]
             self._next_stage = (self._next_stage + 1) % self.STAGES
             stage.set_rows(B)
-            _lib.check(L.ddpb_host_gather(xp, yp, idx.ctypes.data + start * 8, B, self.dx, self.dy,
-                                          stage.host[0].data_ptr(), stage.host[1].data_ptr()), "ddpb_host_gather")
-            yield HostBatch(stage, 0), HostBatch(stage, 1)
+            rc = L.ddpb_host_gather(xp, yp, idx_ptr + start * 8, B, self.dx, self.dy, stage.host_x_ptr, stage.host_y_ptr)
+            if rc:
+                _lib.check(rc, "ddpb_host_gather")
+            yield stage.halves
 
     def _iter_device(self):
         if self._dev is None:

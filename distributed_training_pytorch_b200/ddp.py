@@ -22,12 +22,18 @@ import torch
 import torch.distributed as dist
 
 from . import _lib
-from .data import DeviceBatch, HostBatch
+import ctypes
+
+import numpy as np
+
+from .data import DeviceBatch, HostBatch, StagedBatch
 from .engine import engine_for
 from .toy_model_and_data import ToyModel
 
 _OWNERS = {}          # id(nn.Parameter) -> backend
 LOSS_RING = 1024      # loss slots per model; a LossValue stays readable for this many steps
+LOSS_SENTINEL = 0x7FC0DEAD   # a NaN payload no kernel produces: "slot not written yet"
+LOSS_SPIN_NS = 200_000       # poll this long before falling back to a stream synchronisation
 
 
 def owner_of(param):
@@ -129,8 +135,13 @@ class ToyBackend:
                 _OWNERS[id(p)] = self
                 off += n
             self.state = torch.zeros(4, dtype=torch.int64, device=dev)       # ddpb_opt_state {step, seq, ...}
-            self.loss_ring = torch.zeros(LOSS_RING, dtype=torch.float32, device=dev)
+            # The loss ring lives in pinned host memory that the GPU writes directly (unified
+            # addressing): reading a loss is a poll of one host word, not a copy + stream sync.
             self.loss_host = torch.zeros(LOSS_RING, dtype=torch.float32, pin_memory=True)
+            self.loss_bits = self.loss_host.numpy().view(np.uint32)
+            self.loss_ptr = self.loss_host.data_ptr()
+            self._loss_out = ctypes.c_float()
+            self._loss_out_ref = ctypes.byref(self._loss_out)
             self.m = self.v = None
         self.world, self.rank, self.backend_name = 1, 0, None
         self.process_group = process_group
@@ -147,7 +158,7 @@ class ToyBackend:
         self.job = _lib.ToyJob()
         j = self.job
         j.params, j.grads = self.params.data_ptr(), self.grads.data_ptr()
-        j.state, j.loss_ring, j.loss_ring_n = self.state.data_ptr(), self.loss_ring.data_ptr(), LOSS_RING
+        j.state, j.loss_ring, j.loss_ring_n = self.state.data_ptr(), self.loss_ptr, LOSS_RING
         j.idx_rows, j.idx_stride = 1, 0
         self._out = None
 
@@ -194,15 +205,26 @@ class ToyBackend:
     # -- describing work ---------------------------------------------------------------
     def _bind_batch(self, data, target):
         j = self.job
-        if isinstance(data, HostBatch):
+        if type(data) is HostBatch:
             data = data.cuda(self.device)
-        if isinstance(target, HostBatch):
+        if type(target) is HostBatch:
             target = target.cuda(self.device)
-        if isinstance(data, DeviceBatch):
+        if type(data) is StagedBatch:                       # the loader's own batch: trusted layout, deferred copy
+            stage = data.stage
+            if target is not None and (type(target) is not StagedBatch or target.stage is not stage):
+                raise _lib.DdpB200Error("data and target must come from the same loader batch")
+            j.x, j.y, j.idx, j.B, j.idx_stride, j.n_data = stage.dev_x_ptr, stage.dev_y_ptr, None, stage.B, 0, 0
+            if not stage.copied:
+                self.engine.attach_copy(stage)
+            self.keep = stage
+            return
+        if type(data) is DeviceBatch:
             j.x, j.y, j.idx, j.B = data.x.data_ptr(), data.y.data_ptr(), data.idx_ptr, data.B
             j.idx_stride, j.n_data = data.B, data.x.shape[0]
-            self.keep = [data.keep]
+            self.keep = data.keep
             return
+        if type(target) is StagedBatch:
+            target = target.tensor()
         if not (isinstance(data, torch.Tensor) and data.is_cuda and data.dtype == torch.float32
                 and data.dim() == 2 and data.shape[1] == 2 and data.is_contiguous()):
             raise _lib.DdpB200Error("model input must be a contiguous float32 CUDA tensor [B,2] (or a loader batch)")
@@ -220,7 +242,8 @@ class ToyBackend:
     def _describe(self, loss, mode):
         self._bind_batch(loss.output.data, loss.target)
         self.job.mode = mode
-        loss.slot = self.seq % LOSS_RING
+        slot = loss.slot = self.seq % LOSS_RING
+        self.loss_bits[slot] = LOSS_SENTINEL
         self.seq += 1
         self.grads_fresh = mode == _lib.MODE_GRAD
         self.engine.enqueue(self)
@@ -294,19 +317,19 @@ class ToyBackend:
 
     def read_loss(self, loss):
         """Local mean loss as a 0-dim CPU tensor; blocks like the reference's .cpu() (demo.py:115)."""
-        self._ensure_described(loss)
-        self.engine.flush()
-        lib, stream = self.engine.lib, self.engine.stream()
-        off = 4 * loss.slot
-        _lib.check(lib.ddpb_memcpy_d2h_async(self.loss_host.data_ptr() + off, self.loss_ring.data_ptr() + off, 4, stream),
-                   "ddpb_memcpy_d2h_async")
-        _lib.check(lib.ddpb_stream_sync(stream), "ddpb_stream_sync")
-        return self.loss_host[loss.slot].clone()
+        if loss.slot is None:
+            self._ensure_described(loss)
+        eng = self.engine
+        if eng.queue:
+            eng.flush()
+        rc = eng.lib.ddpb_wait_f32(self.loss_ptr + 4 * loss.slot, LOSS_SENTINEL, LOSS_SPIN_NS, eng.last_stream,
+                                   self._loss_out_ref)
+        if rc:
+            _lib.check(rc, "ddpb_wait_f32")
+        return torch.tensor(self._loss_out.value)
 
     def loss_device_view(self, loss):
-        self._ensure_described(loss)
-        self.engine.flush()
-        return self.loss_ring[loss.slot]
+        return self.read_loss(loss).to(self.device)
 
     def forward_now(self, data):
         """Eager forward (MODE_FWD) for callers that want the output values."""

@@ -43,6 +43,8 @@ class Engine:
         self.queue = []                                    # FlatModel objects with a described, unlaunched job
         self.jobs = (_lib.ToyJob * _lib.MAX_JOBS)()
         self.launches = 0                                  # kernels this engine has launched (bench: gpu_launches)
+        self.pending_copy = None                           # a data._Stage whose H2D copy rides with the next launch
+        self.last_stream = None                            # stream of the most recent launch
         self.comm = None                                   # NCCL communicator handle (void*)
         self.comm_rank, self.comm_world = 0, 1
 
@@ -61,15 +63,34 @@ class Engine:
         if len(self.queue) == _lib.MAX_JOBS:
             self.flush()
 
+    def attach_copy(self, stage):
+        """The next launch copies `stage` (pinned (x|y) block) to its device twin first."""
+        if self.pending_copy is not None and self.pending_copy is not stage:
+            self.pending_copy.copy_now()
+        self.pending_copy = stage
+
+    def drop_pending_copy(self, stage):
+        if self.pending_copy is stage:
+            self.pending_copy = None
+
     def flush(self):
         """Launch everything described so far (one kernel for all pending toy jobs)."""
         if not self.queue:
             return
         batch, self.queue = self.queue, []
+        jobs = self.jobs
         for i, model in enumerate(batch):
-            self.jobs[i] = model.job
-        stream = self.stream()
-        _lib.check(self.lib.ddpb_toy_step(self.jobs, len(batch), stream), "ddpb_toy_step")
+            jobs[i] = model.job
+        stream = self.last_stream = self.stream()
+        stage = self.pending_copy
+        if stage is not None and not stage.copied:
+            rc = self.lib.ddpb_toy_step_h2d(jobs, len(batch), stage.dev_x_ptr, stage.host_ptr, stage.nbytes, stream)
+            stage.copied = True
+        else:
+            rc = self.lib.ddpb_toy_step(jobs, len(batch), stream)
+        self.pending_copy = None
+        if rc:
+            _lib.check(rc, "ddpb_toy_step")
         self.launches += 1
         for model in batch:
             model.after_launch(stream)

@@ -66,7 +66,7 @@ class LossValue:
         return self.device_tensor()
 
     def device_tensor(self):
-        """0-dim CUDA tensor view of the loss slot (valid until the ring wraps)."""
+        """0-dim CUDA tensor holding the loss."""
         return self._loss.backend.loss_device_view(self._loss)
 
     # wandb.log({'loss/loss': loss.detach()}) (demo_one_model_multi_gpu.py:130) stringifies / converts

@@ -110,6 +110,10 @@ typedef struct ddpb_toy_job {
 } ddpb_toy_job;
 
 int ddpb_toy_step(const ddpb_toy_job *jobs /* host */, int njobs, void *stream);
+/* The same launch preceded, on the same stream, by one pinned-host -> device copy: the
+ * `data.cuda(); target.cuda()` of demo.py:102-103 and the step in one host call. */
+int ddpb_toy_step_h2d(const ddpb_toy_job *jobs, int njobs, void *dst_dev, const void *src_host,
+                      int64_t bytes, void *stream);
 
 /* ---- optimizer over a flat bucket ----------------------------------------- */
 /* One pass over a (reduced) gradient bucket: g = bucket * grad_scale (the 1/W of
@@ -145,6 +149,10 @@ int ddpb_allreduce_sum_f32(void *comm, float *buf, int64_t n, void *stream);
 
 /* ---- streams / events helpers the host layer needs without torch calls ----- */
 int ddpb_stream_sync(void *stream);
+/* Blocks until *host_slot (pinned, device-mapped memory a kernel writes, e.g. a loss_ring slot)
+ * no longer holds `sentinel_bits`; after spin_ns of polling it synchronises the stream
+ * instead.  Replaces the blocking loss.detach().cpu() of demo.py:115,117. */
+int ddpb_wait_f32(const float *host_slot, uint32_t sentinel_bits, int64_t spin_ns, void *stream, float *out);
 int ddpb_memcpy_h2d_async(void *dst_dev, const void *src_host, int64_t bytes, void *stream);
 int ddpb_memcpy_d2h_async(void *dst_host, const void *src_dev, int64_t bytes, void *stream);
 
