@@ -266,6 +266,7 @@ def ours(args):
         jobs = (_lib.ToyJob * _lib.MAX_JOBS)()
         for i, m in enumerate((model_X, model_Y)):
             j = m._backend.job
+            j.loss_ring = m._backend.loss_dev.data_ptr()          # nobody reads losses in this loop: keep them in HBM
             j.x, j.y, j.idx = loader._dev[0].data_ptr(), loader._dev[1].data_ptr(), rows.data_ptr()
             j.idx_rows, j.idx_stride, j.B, j.mode, j.n_data = n_rows, BATCH, BATCH, _lib.MODE_STEP, DATASET
             jobs[i] = j

@@ -42,6 +42,7 @@ _SIGNATURES = {
     "ddpb_randperm": (c_int, [c_uint64, c_int64, c_void_p]),
     "ddpb_sampler_indices": (c_int64, [c_int64, c_int, c_int, c_int, c_uint64, c_uint64, c_int, c_void_p, c_int64]),
     "ddpb_sampler_epochs_i32": (c_int, [c_int64, c_int, c_int, c_int, c_uint64, c_uint64, c_int, c_int, c_void_p, c_int64]),
+    "ddpb_sampler_epochs_i64": (c_int, [c_int64, c_int, c_int, c_int, c_uint64, c_uint64, c_int, c_int, c_void_p, c_int64]),
     "ddpb_host_gather": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p, c_void_p]),
     "ddpb_gather_batch": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "ddpb_toy_step": (c_int, [c_void_p, c_int, c_void_p]),

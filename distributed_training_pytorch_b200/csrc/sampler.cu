@@ -108,6 +108,25 @@ DDPB_API int ddpb_sampler_epochs_i32(int64_t n, int world, int rank, int shuffle
     return 0;
 }
 
+// int64 rows for `nepochs` consecutive epochs in one call (the host loader refills its cache
+// with this instead of paying one foreign-function call per epoch).
+DDPB_API int ddpb_sampler_epochs_i64(int64_t n, int world, int rank, int shuffle, uint64_t seed,
+                                     uint64_t epoch0, int nepochs, int drop_last, int64_t *out, int64_t stride) {
+    DDPB_REQUIRE(n > 0 && n < kMaxPerm && world > 0 && rank >= 0 && rank < world && out && nepochs >= 0,
+                 "ddpb_sampler_epochs_i64: bad arguments");
+    const int64_t per_rank = samples_per_rank(n, world, drop_last);
+    DDPB_REQUIRE(stride >= per_rank, "ddpb_sampler_epochs_i64: stride %lld < %lld indices per epoch",
+                 (long long)stride, (long long)per_rank);
+    std::vector<int64_t> order((size_t)n);
+    for (int e = 0; e < nepochs; ++e) {
+        if (shuffle) shuffled_range(seed + epoch0 + (uint64_t)e, n, order.data());
+        else for (int64_t i = 0; i < n; ++i) order[(size_t)i] = i;
+        int64_t *row = out + (int64_t)e * stride;
+        for (int64_t k = 0; k < per_rank; ++k) row[k] = order[(size_t)((rank + k * world) % n)];
+    }
+    return 0;
+}
+
 DDPB_API int ddpb_host_gather(const float *X, const float *Y, const int64_t *idx, int64_t B, int dx, int dy,
                               float *outX, float *outY) {
     DDPB_REQUIRE(X && Y && idx && outX && outY && B >= 0 && dx > 0 && dy > 0, "ddpb_host_gather: bad arguments");

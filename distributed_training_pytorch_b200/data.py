@@ -40,6 +40,22 @@ class DistributedSampler:
             self.num_samples = math.ceil(n / num_replicas)
         self.total_size = self.num_samples * self.num_replicas
 
+    CACHE_EPOCHS = 64
+
+    def cached_indices(self):
+        """Indices of the current epoch from a block of CACHE_EPOCHS epochs computed in one native
+        call (bit-identical to indices(); amortises the per-epoch call overhead)."""
+        cache = getattr(self, "_cache", None)
+        e = self.epoch
+        if cache is None or not (cache[0] <= e < cache[0] + self.CACHE_EPOCHS) or cache[2] != (self.seed, self.shuffle):
+            rows = np.empty((self.CACHE_EPOCHS, self.num_samples), np.int64)
+            _lib.check(_lib.lib().ddpb_sampler_epochs_i64(len(self.dataset), self.num_replicas, self.rank,
+                                                          int(self.shuffle), self.seed, e, self.CACHE_EPOCHS,
+                                                          int(self.drop_last), rows.ctypes.data, self.num_samples),
+                       "ddpb_sampler_epochs_i64")
+            cache = self._cache = (e, rows, (self.seed, self.shuffle))
+        return cache[1][e - cache[0]]
+
     def indices(self, epoch=None):
         """int64 numpy array of this rank's indices for `epoch` (default: the current one)."""
         out = np.empty(self.num_samples, np.int64)
@@ -272,6 +288,8 @@ class DataLoader:
     def _indices(self):
         if self.sampler is None:
             return np.arange(len(self.dataset), dtype=np.int64)
+        if hasattr(self.sampler, "cached_indices"):
+            return self.sampler.cached_indices()
         if hasattr(self.sampler, "indices"):
             return self.sampler.indices()
         return np.fromiter(iter(self.sampler), dtype=np.int64)
@@ -283,18 +301,20 @@ class DataLoader:
         if self._stages is None:
             self._stages = [_Stage(self.batch_size, self.dx, self.dy) for _ in range(self.STAGES)]
         idx = self._indices()
-        L = _lib.lib()
-        xp, yp, idx_ptr = self.x.data_ptr(), self.y.data_ptr(), idx.ctypes.data
-        for start in range(0, len(idx), self.batch_size):
-            B = min(self.batch_size, len(idx) - start)
-            if B < self.batch_size and self.drop_last:
+        n, bs = len(idx), self.batch_size
+        gather = _lib.lib().ddpb_host_gather
+        xp, yp, idx_ptr, dx, dy = self.x.data_ptr(), self.y.data_ptr(), idx.ctypes.data, self.dx, self.dy
+        stages, nstages = self._stages, self.STAGES
+        for start in range(0, n, bs):
+            B = min(bs, n - start)
+            if B < bs and self.drop_last:
                 return
-            stage = self._stages[self._next_stage]
-            self._next_stage = (self._next_stage + 1) % self.STAGES
+            k = self._next_stage
+            stage = stages[k]
+            self._next_stage = k + 1 if k + 1 < nstages else 0
             stage.set_rows(B)
-            rc = L.ddpb_host_gather(xp, yp, idx_ptr + start * 8, B, self.dx, self.dy, stage.host_x_ptr, stage.host_y_ptr)
-            if rc:
-                _lib.check(rc, "ddpb_host_gather")
+            if gather(xp, yp, idx_ptr + start * 8, B, dx, dy, stage.host_x_ptr, stage.host_y_ptr):
+                _lib.check(1, "ddpb_host_gather")
             yield stage.halves
 
     def _iter_device(self):

@@ -137,6 +137,9 @@ class ToyBackend:
             self.state = torch.zeros(4, dtype=torch.int64, device=dev)       # ddpb_opt_state {step, seq, ...}
             # The loss ring lives in pinned host memory that the GPU writes directly (unified
             # addressing): reading a loss is a poll of one host word, not a copy + stream sync.
+            # A loop that never reads its losses keeps them in HBM instead (a kernel whose last
+            # store crosses PCIe retires ~2 us later, which a graph-replayed step would feel).
+            self.loss_dev = torch.zeros(LOSS_RING, dtype=torch.float32, device=dev)
             self.loss_host = torch.zeros(LOSS_RING, dtype=torch.float32, pin_memory=True)
             self.loss_bits = self.loss_host.numpy().view(np.uint32)
             self.loss_ptr = self.loss_host.data_ptr()
@@ -152,6 +155,8 @@ class ToyBackend:
         self.lazy = (self.world == 1) if lazy_step is None else bool(lazy_step) and self.world == 1
         self.opt_kind, self.hyper = None, None
         self.seq = 0                    # host mirror of state.seq
+        self.unread = 0                 # losses described since the last one was read
+        self.ring_on_host = True
         self.waiting = None             # Loss whose backward() was called and not yet described
         self.grads_fresh = False        # a GRAD job was described; an optimizer step may consume it
         self.keep = []                  # tensors referenced by the described job
@@ -243,7 +248,13 @@ class ToyBackend:
         self._bind_batch(loss.output.data, loss.target)
         self.job.mode = mode
         slot = loss.slot = self.seq % LOSS_RING
-        self.loss_bits[slot] = LOSS_SENTINEL
+        if self.unread > 8:                      # nobody has been reading losses: keep them on the device
+            if self.ring_on_host:
+                self.ring_on_host, self.job.loss_ring = False, self.loss_dev.data_ptr()
+        else:
+            self.unread += 1
+            self.loss_bits[slot] = LOSS_SENTINEL
+        loss.on_host = self.ring_on_host
         self.seq += 1
         self.grads_fresh = mode == _lib.MODE_GRAD
         self.engine.enqueue(self)
@@ -322,6 +333,14 @@ class ToyBackend:
         eng = self.engine
         if eng.queue:
             eng.flush()
+        self.unread = 0
+        if not self.ring_on_host:                # from the next step on, losses go straight to host memory again
+            self.ring_on_host, self.job.loss_ring = True, self.loss_ptr
+        if not loss.on_host:                     # this one was written to HBM: copy it out the classic way
+            off = 4 * loss.slot
+            _lib.check(eng.lib.ddpb_memcpy_d2h_async(self.loss_ptr + off, self.loss_dev.data_ptr() + off, 4, eng.last_stream), "d2h")
+            _lib.check(eng.lib.ddpb_stream_sync(eng.last_stream), "ddpb_stream_sync")
+            return self.loss_host[loss.slot].clone()
         rc = eng.lib.ddpb_wait_f32(self.loss_ptr + 4 * loss.slot, LOSS_SENTINEL, LOSS_SPIN_NS, eng.last_stream,
                                    self._loss_out_ref)
         if rc:

@@ -45,12 +45,24 @@ class Engine:
         self.launches = 0                                  # kernels this engine has launched (bench: gpu_launches)
         self.pending_copy = None                           # a data._Stage whose H2D copy rides with the next launch
         self.last_stream = None                            # stream of the most recent launch
+        self._stream = None
         self.comm = None                                   # NCCL communicator handle (void*)
         self.comm_rank, self.comm_world = 0, 1
 
     # -- streams -------------------------------------------------------------
     def stream(self):
-        return torch.cuda.current_stream(self.device).cuda_stream
+        """cudaStream_t the engine launches on: torch's current stream of the device when the
+        engine was created (normally the default stream), cached because querying torch costs
+        more than describing a whole step.  Call use_stream() to move the engine elsewhere."""
+        s = self._stream
+        if s is None:
+            s = self._stream = torch.cuda.current_stream(self.device).cuda_stream
+        return s
+
+    def use_stream(self, stream=None):
+        """Launch on `stream` (a torch.cuda.Stream) from now on; None = re-read torch's current stream."""
+        self.flush()
+        self._stream = None if stream is None else stream.cuda_stream
 
     def sync(self):
         _lib.check(self.lib.ddpb_stream_sync(self.stream()), "ddpb_stream_sync")

@@ -25,7 +25,8 @@ class Loss:
     def __init__(self, output, target):
         self.output, self.target = output, target
         self.backend = output.backend
-        self.slot = None           # (flat model, ring slot) once described to the engine
+        self.slot = None           # ring slot once described to the engine
+        self.on_host = True        # whether that slot is in the pinned host ring or the HBM ring
         self.backward_called = False
 
     # -- autograd-like surface ----------------------------------------------

@@ -52,6 +52,11 @@ int ddpb_sampler_epochs_i32(int64_t n, int world, int rank, int shuffle, uint64_
                             uint64_t epoch0, int nepochs, int drop_last,
                             int32_t *out /* host [nepochs*stride] */, int64_t stride);
 
+/* int64 variant for the host loader's epoch cache. */
+int ddpb_sampler_epochs_i64(int64_t n, int world, int rank, int shuffle, uint64_t seed,
+                            uint64_t epoch0, int nepochs, int drop_last,
+                            int64_t *out /* host [nepochs*stride] */, int64_t stride);
+
 /* ---- batch assembly ------------------------------------------------------- */
 /* Host: replaces ToyData.__getitem__ x B + default_collate (toy_model_and_data.py:32-33,
  * demo.py:99) by one gather from the dense dataset into (pinned) staging rows. */
