@@ -14,6 +14,10 @@ c_float, c_double, c_char_p = ctypes.c_float, ctypes.c_double, ctypes.c_char_p
 MODE_FWD, MODE_GRAD, MODE_STEP = 0, 1, 2
 OPT_ADAM, OPT_SGD = 0, 1
 MAX_JOBS = 4
+MAX_PEERS = 8
+XCHG_ROW = 376
+XCHG_DATA_FLOATS = 2 * MAX_PEERS * XCHG_ROW
+XCHG_FLAG_WORDS = 2 * MAX_PEERS * 8
 TOY_HIDDEN, TOY_PARAMS = 10, 371
 
 
@@ -32,7 +36,9 @@ class ToyJob(ctypes.Structure):
                 ("B", c_int32), ("mode", c_int32), ("opt", c_int32), ("loss_ring_n", c_int32),
                 ("idx_rows", c_int32), ("idx_stride", c_int32), ("bias_table_n", c_int32), ("n_data", c_int32),
                 ("lr", c_double), ("beta1", c_double), ("beta2", c_double), ("eps", c_double),
-                ("momentum", c_double)]
+                ("momentum", c_double),
+                ("peer_data", c_void_p * 8), ("peer_flags", c_void_p * 8),
+                ("world", c_int32), ("rank", c_int32), ("inv_world", c_float), ("reserved2", c_int32)]
 
 
 _SIGNATURES = {
@@ -63,6 +69,11 @@ _SIGNATURES = {
     "ddpb_graph_end": (c_int, [c_void_p, c_void_p]),
     "ddpb_graph_launch": (c_int, [c_void_p, c_void_p]),
     "ddpb_graph_destroy": (c_int, [c_void_p]),
+    "ddpb_peer_alloc": (c_int, [c_int64, c_void_p, c_void_p]),
+    "ddpb_peer_open": (c_int, [c_void_p, c_void_p]),
+    "ddpb_peer_close": (c_int, [c_void_p]),
+    "ddpb_peer_free": (c_int, [c_void_p]),
+    "ddpb_enable_peer": (c_int, [c_int, c_int]),
     "ddpb_stream_sync": (c_int, [c_void_p]),
     "ddpb_memcpy_h2d_async": (c_int, [c_void_p, c_void_p, c_int64, c_void_p]),
     "ddpb_memcpy_d2h_async": (c_int, [c_void_p, c_void_p, c_int64, c_void_p]),

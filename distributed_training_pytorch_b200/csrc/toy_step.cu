@@ -69,6 +69,7 @@ constexpr int R_DZ = R_ZERO + 1;                 // dz_0 .. dz_3, then dz_4
 constexpr int kRows = R_DZ + 4 * HP + 1;
 constexpr int kSlice = (P + 1 + kCluster - 1) / kCluster;   // 47 values per CTA (371 grads + loss sum)
 constexpr int kInboxRow = 48;
+constexpr int kXchgRow = DDPB_XCHG_ROW;          // floats per (parity, source rank) row of a peer window
 constexpr int kMaxStagedRows = 1024;             // datasets up to this many rows are staged in shared memory
 constexpr int kStageX = (2 * kMaxStagedRows / 4 + kThreads - 1) / kThreads;   // float4 loads per thread
 constexpr int kStageY = (kMaxStagedRows / 4 + kThreads - 1) / kThreads;
@@ -118,6 +119,16 @@ __device__ __forceinline__ unsigned wrap_index(long long seq, int n) {
 }
 
 __device__ __forceinline__ void compute_barrier() { asm volatile("bar.sync 1, %0;" ::"n"(kComputeThreads) : "memory"); }
+
+__device__ __forceinline__ void optimizer_barrier() {
+    asm volatile("bar.sync 2, %0;" ::"n"(kThreads - kComputeThreads) : "memory");
+}
+
+// System-scope accesses to peer-mapped windows (other GPUs' HBM over NVLink, or our own).
+__device__ __forceinline__ void st_relaxed_sys(float *p, float v) { asm volatile("st.relaxed.sys.global.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory"); }
+__device__ __forceinline__ float ld_relaxed_sys(const float *p) { float v; asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory"); return v; }
+__device__ __forceinline__ void st_release_sys(unsigned *p, unsigned v) { asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
+__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned *p) { unsigned v; asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory"); return v; }
 
 __device__ __forceinline__ unsigned smem_addr(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
 
@@ -245,6 +256,7 @@ toy_step_kernel(const __grid_constant__ JobList jl) {
     // on demand through a dynamically indexed reference chained 17 LDC -> compare -> branch
     // round trips (~1000 cycles before the first useful instruction, seen in the timeline).
     const ddpb_toy_job job = jl.jobs[blockIdx.y];
+    const ddpb_toy_job &jref = jl.jobs[blockIdx.y];     // the peer pointer arrays stay in the constant bank
     cg::cluster_group cluster = cg::this_cluster();
     const int cta = (int)cluster.block_rank();
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -256,7 +268,7 @@ toy_step_kernel(const __grid_constant__ JobList jl) {
     const float *__restrict__ prm = job.params;
     const float pv0 = prm[tid];                                   // 371 parameters over 192 threads
     const float pv1 = (tid + kThreads < P) ? prm[tid + kThreads] : 0.f;
-    const bool need_seq = mode != DDPB_MODE_FWD && (job.loss_ring_n > 1 || (job.idx && job.idx_rows > 1));
+    const bool need_seq = mode != DDPB_MODE_FWD && (job.loss_ring_n > 1 || (job.idx && job.idx_rows > 1) || job.world > 1);
     const long long seq = (job.state && need_seq) ? job.state->seq : 0;
 
     const int own = cta * kSlice + (tid - kComputeThreads);     // index into the 372-entry slice table
@@ -356,14 +368,51 @@ toy_step_kernel(const __grid_constant__ JobList jl) {
         const float inv_B = __fdiv_rn(1.0f, (float)B);
         mbar_wait(&S.mbar, 0);                            // all eight CTAs have pushed their partials
         DDPB_STAMP(3);
+        const int slot = tid - kComputeThreads;
+        float total = 0.f;
         if (owner) {
-            const int slot = tid - kComputeThreads;
-            float total = 0.f;
 #pragma unroll
             for (int c = 0; c < kCluster; ++c) total += S.inbox[c][slot];
+            if (own == P && loss_slot)                                       // local mean loss (what loss.cpu() returns)
+                *loss_slot = (B & (B - 1)) == 0 ? total * inv_B : __fdiv_rn(total, (float)B);
+        }
+        if (job.world > 1 && mode == DDPB_MODE_STEP) {
+            // ---- one-shot all-reduce over NVLink, fused into the step (no NCCL launch, no second
+            // kernel): slice c of every rank's bucket meets in every rank's receive window.
+            // DDP's arithmetic: scale by 1/W first, then sum (default_hooks.py:24-29); ranks are
+            // summed in ascending order on every GPU, so replicas stay bit-identical.
+            const unsigned xseq = (unsigned)seq + 1u;                        // this exchange's ticket
+            const int par = (int)(seq & 1);                                  // double-buffered windows
+            const int W = job.world, me = job.rank;
+            const float contrib = (own < P) ? __fmul_rn(total, job.inv_world) : total;
+            if (owner) {
+                const size_t at = (size_t)(par * DDPB_MAX_PEERS + me) * kXchgRow + own;
+                for (int dst = 0; dst < W; ++dst) st_relaxed_sys(jref.peer_data[dst] + at, contrib);
+                __threadfence_system();
+            }
+            optimizer_barrier();
+            if (slot < W)                                                    // publish: one flag per destination
+                st_release_sys(jref.peer_flags[slot] + (par * DDPB_MAX_PEERS + me) * kCluster + cta, xseq);
+            if (slot < W) {                                                  // wait for rank `slot`'s slice
+                const unsigned *flag = jref.peer_flags[me] + (par * DDPB_MAX_PEERS + slot) * kCluster + cta;
+                long long spins = 0;
+                while (ld_acquire_sys(flag) != xseq) {
+                    if (++spins > (1ll << 26)) {                             // ~1 s: a peer died; fail loudly, do not hang
+                        job.state->reserved[0] = 1;
+                        break;
+                    }
+                }
+            }
+            optimizer_barrier();
+            if (owner) {
+                total = 0.f;
+                const float *mine = jref.peer_data[me] + (size_t)(par * DDPB_MAX_PEERS) * kXchgRow + own;
+                for (int src = 0; src < W; ++src) total += ld_relaxed_sys(mine + (size_t)src * kXchgRow);
+            }
+        }
+        if (owner) {
             if (own == P) {
-                g_out[P] = total;                                            // sum (o-t)^2 over the local batch
-                if (loss_slot) *loss_slot = (B & (B - 1)) == 0 ? total * inv_B : __fdiv_rn(total, (float)B);
+                g_out[P] = total;                                            // sum (o-t)^2 (over all ranks when W > 1)
             } else {
                 g_out[own] = total;
                 if (mode == DDPB_MODE_STEP) {
@@ -557,6 +606,12 @@ static int launch_toy_step(const ddpb_toy_job *jobs, int njobs, cudaStream_t str
         }
         if (q.loss_ring) DDPB_REQUIRE(q.loss_ring_n >= 1, "ddpb_toy_step: job %d: empty loss ring", j);
         if (q.idx) DDPB_REQUIRE(q.idx_rows >= 1 && q.idx_stride >= q.B, "ddpb_toy_step: job %d: index rows too short", j);
+        if (q.world > 1 && q.mode == DDPB_MODE_STEP) {
+            DDPB_REQUIRE(q.world <= DDPB_MAX_PEERS && q.rank >= 0 && q.rank < q.world,
+                         "ddpb_toy_step: job %d: world %d / rank %d outside the %d-peer exchange", j, q.world, q.rank, DDPB_MAX_PEERS);
+            for (int r = 0; r < q.world; ++r)
+                DDPB_REQUIRE(q.peer_data[r] && q.peer_flags[r], "ddpb_toy_step: job %d: peer window %d not mapped", j, r);
+        }
         jl.jobs[j] = q;
         // the shared-memory staging of a small dataset needs whole, aligned float4 rows
         if (!q.idx || q.n_data < 0 || (q.n_data & 3) || ((uintptr_t)q.x & 15) || ((uintptr_t)q.y & 15)) jl.jobs[j].n_data = 0;

@@ -112,3 +112,53 @@ DDPB_API int ddpb_wait_f32(const float *host_slot, uint32_t sentinel_bits, int64
     *out = cvt.f;
     return 0;
 }
+
+// ---- peer windows ------------------------------------------------------------------------
+DDPB_API int ddpb_peer_alloc(int64_t bytes, void **ptr_out, char handle_out[64]) {
+    DDPB_REQUIRE(bytes > 0 && ptr_out && handle_out, "ddpb_peer_alloc: bad arguments");
+    void *p = nullptr;
+    DDPB_CUDA(cudaMalloc(&p, (size_t)bytes));
+    DDPB_CUDA(cudaMemset(p, 0, (size_t)bytes));
+    DDPB_CUDA(cudaDeviceSynchronize());
+    cudaIpcMemHandle_t h;
+    DDPB_CUDA(cudaIpcGetMemHandle(&h, p));
+    static_assert(sizeof(h) == 64, "IPC handle size");
+    memcpy(handle_out, &h, 64);
+    *ptr_out = p;
+    return 0;
+}
+
+DDPB_API int ddpb_peer_open(const char handle[64], void **ptr_out) {
+    DDPB_REQUIRE(handle && ptr_out, "ddpb_peer_open: bad arguments");
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, 64);
+    DDPB_CUDA(cudaIpcOpenMemHandle(ptr_out, h, cudaIpcMemLazyEnablePeerAccess));
+    return 0;
+}
+
+DDPB_API int ddpb_peer_close(void *mapped_ptr) {
+    if (mapped_ptr) DDPB_CUDA(cudaIpcCloseMemHandle(mapped_ptr));
+    return 0;
+}
+
+DDPB_API int ddpb_peer_free(void *ptr) {
+    if (ptr) DDPB_CUDA(cudaFree(ptr));
+    return 0;
+}
+
+DDPB_API int ddpb_enable_peer(int dev_a, int dev_b) {
+    int prev = 0;
+    DDPB_CUDA(cudaGetDevice(&prev));
+    for (int pass = 0; pass < 2; ++pass) {
+        const int from = pass ? dev_b : dev_a, to = pass ? dev_a : dev_b;
+        int can = 0;
+        DDPB_CUDA(cudaDeviceCanAccessPeer(&can, from, to));
+        if (!can) return ddpb::fail(4, "ddpb_enable_peer: device %d cannot access device %d", from, to);
+        DDPB_CUDA(cudaSetDevice(from));
+        cudaError_t e = cudaDeviceEnablePeerAccess(to, 0);
+        if (e == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
+        else if (e != cudaSuccess) return ddpb::cuda_fail(e, "cudaDeviceEnablePeerAccess", __FILE__, __LINE__);
+    }
+    DDPB_CUDA(cudaSetDevice(prev));
+    return 0;
+}

@@ -23,6 +23,7 @@ import torch.distributed as dist
 
 from . import _lib
 import ctypes
+import os
 
 import numpy as np
 
@@ -103,6 +104,7 @@ class DistributedDataParallel:
     def flat_parameters(self):
         """The flat fp32 parameter vector (after everything described so far has been launched)."""
         self._backend.engine.flush()
+        self._backend.check_peers()
         return self._backend.params
 
 
@@ -152,6 +154,8 @@ class ToyBackend:
             self.world, self.rank = dist.get_world_size(process_group), dist.get_rank(process_group)
             self.backend_name = dist.get_backend(process_group)
         self._sync_replicas()
+        self.fused_exchange = False     # W > 1: gradient all-reduce fused into the step kernel (peer windows)
+        self.peer = None
         self.lazy = (self.world == 1) if lazy_step is None else bool(lazy_step) and self.world == 1
         self.opt_kind, self.hyper = None, None
         self.seq = 0                    # host mirror of state.seq
@@ -165,7 +169,10 @@ class ToyBackend:
         j.params, j.grads = self.params.data_ptr(), self.grads.data_ptr()
         j.state, j.loss_ring, j.loss_ring_n = self.state.data_ptr(), self.loss_ptr, LOSS_RING
         j.idx_rows, j.idx_stride = 1, 0
+        j.world, j.rank, j.inv_world = 1, 0, 1.0
         self._out = None
+        if self.world > 1 and os.environ.get("DDPB_ALLREDUCE", "p2p") == "p2p" and lazy_step is not False:
+            self._map_peer_windows()
 
     # -- construction-time collective (demo.py:70,72) --------------------------------
     def _sync_replicas(self):
@@ -183,6 +190,53 @@ class ToyBackend:
             host = self.params.cpu()
             dist.broadcast(host, src=0, group=self.process_group)
             self.params.copy_(host)
+
+    def _map_peer_windows(self):
+        """Allocate this rank's exchange window, trade IPC handles through the process group and
+        map every peer's window (all ranks of the group must share one NVLink/NVSwitch box)."""
+        if self.world > _lib.MAX_PEERS:
+            return
+        lib = self.engine.lib
+        data_bytes, flag_bytes = _lib.XCHG_DATA_FLOATS * 4, _lib.XCHG_FLAG_WORDS * 4
+        mine, handle = ctypes.c_void_p(), ctypes.create_string_buffer(64)
+        with torch.cuda.device(self.device):
+            _lib.check(lib.ddpb_peer_alloc(data_bytes + flag_bytes, ctypes.byref(mine), handle), "ddpb_peer_alloc")
+            import socket
+            handles = [None] * self.world
+            dist.all_gather_object(handles, (socket.gethostname(), handle.raw), group=self.process_group)
+            ok = all(h[0] == handles[0][0] for h in handles)
+            mapped = []
+            if ok:
+                for r, (_, raw) in enumerate(handles):
+                    if r == self.rank:
+                        mapped.append(mine.value)
+                        continue
+                    ptr = ctypes.c_void_p()
+                    if lib.ddpb_peer_open(raw, ctypes.byref(ptr)) != 0:
+                        ok = False
+                        break
+                    mapped.append(ptr.value)
+            agree = [None] * self.world
+            dist.all_gather_object(agree, bool(ok), group=self.process_group)
+        if not all(agree):                       # no peer access somewhere: every rank falls back to NCCL together
+            for r, ptr in enumerate(mapped):
+                if r != self.rank:
+                    lib.ddpb_peer_close(ptr)
+            lib.ddpb_peer_free(mine)
+            return
+        self.peer = dict(mine=mine, mapped=mapped)
+        j = self.job
+        for r, ptr in enumerate(mapped):
+            j.peer_data[r] = ptr
+            j.peer_flags[r] = ptr + data_bytes
+        j.world, j.rank, j.inv_world = self.world, self.rank, 1.0 / self.world
+        self.fused_exchange = True
+        self.lazy = True
+
+    def check_peers(self):
+        """Raise if a fused exchange timed out waiting for a peer (state.reserved[0] set by the kernel)."""
+        if self.fused_exchange and int(self.state[2].item()) != 0:
+            raise _lib.DdpB200Error("a peer GPU did not deliver its gradient slice in time (fused all-reduce timed out)")
 
     # -- optimizer binding -----------------------------------------------------------
     def attach_optimizer(self, kind, hyper):
@@ -258,7 +312,7 @@ class ToyBackend:
         self.seq += 1
         self.grads_fresh = mode == _lib.MODE_GRAD
         self.engine.enqueue(self)
-        if self.world > 1:
+        if self.world > 1 and mode == _lib.MODE_GRAD:
             self.engine.flush()           # start the bucket all-reduce now: it overlaps whatever the host does next
 
     def after_launch(self, stream):

@@ -30,6 +30,10 @@ extern "C" {
 #define DDPB_TOY_HIDDEN 10         /* toy_model_and_data.py:13-21 */
 #define DDPB_TOY_PARAMS 371        /* 3H^2 + 7H + 1 */
 #define DDPB_MAX_JOBS 4            /* models per ddpb_toy_step launch */
+#define DDPB_MAX_PEERS 8           /* GPUs of one NVSwitch box taking part in the fused exchange */
+#define DDPB_XCHG_ROW 376          /* floats per (parity, source rank) row of a peer window (372 used) */
+#define DDPB_XCHG_DATA_FLOATS (2 * DDPB_MAX_PEERS * DDPB_XCHG_ROW)   /* one model's data window */
+#define DDPB_XCHG_FLAG_WORDS (2 * DDPB_MAX_PEERS * 8)                /* one model's flag window */
 
 /* ---- introspection ------------------------------------------------------- */
 int ddpb_version(void);
@@ -112,6 +116,17 @@ typedef struct ddpb_toy_job {
     int32_t bias_table_n;
     int32_t n_data;           /* rows of the dataset behind idx (0 = unknown): <= 1024 rows are staged on chip */
     double lr, beta1, beta2, eps, momentum;
+    /* world > 1 with DDPB_MODE_STEP: the gradient all-reduce (demo.py:107,109 via the c10d reducer)
+     * is fused into the step as a one-shot exchange over peer-mapped windows (NVLink P2P stores):
+     * peer_data[r] / peer_flags[r] are rank r's windows as mapped into THIS process
+     * (ddpb_peer_alloc / ddpb_peer_open), zero-initialised, DDPB_XCHG_DATA_FLOATS floats and
+     * DDPB_XCHG_FLAG_WORDS words each; entry [rank] is this rank's own window.  state->seq must
+     * advance in lock step on all ranks; state->reserved[0] != 0 afterwards = a peer timed out. */
+    float *peer_data[DDPB_MAX_PEERS];
+    uint32_t *peer_flags[DDPB_MAX_PEERS];
+    int32_t world, rank;
+    float inv_world;          /* 1/world (DDP's div factor) */
+    int32_t reserved2;
 } ddpb_toy_job;
 
 int ddpb_toy_step(const ddpb_toy_job *jobs /* host */, int njobs, void *stream);
@@ -151,6 +166,19 @@ int ddpb_comm_create(const char id[128], int rank, int world, int device, void *
 int ddpb_comm_destroy(void *comm);
 int ddpb_broadcast_f32(void *comm, float *buf, int64_t n, int root, void *stream);
 int ddpb_allreduce_sum_f32(void *comm, float *buf, int64_t n, void *stream);
+
+/* ---- peer windows (same box, one process per GPU or one process, several GPUs) ---- */
+/* cudaMalloc'ed + zeroed window of `bytes` on the current device and its 64-byte IPC handle;
+ * other processes map it with ddpb_peer_open (peer access is enabled lazily by the driver),
+ * the same process on another GPU with ddpb_enable_peer + the raw pointer.  The library owns
+ * these allocations (they cannot come from PyTorch's caching allocator: IPC handles cover
+ * whole cudaMalloc blocks). */
+int ddpb_peer_alloc(int64_t bytes, void **ptr_out, char handle_out[64]);
+int ddpb_peer_open(const char handle[64], void **ptr_out);
+int ddpb_peer_close(void *mapped_ptr);
+int ddpb_peer_free(void *ptr);
+/* cudaDeviceEnablePeerAccess in both directions (model-parallel demo: demo_one_model_multi_gpu.py:41). */
+int ddpb_enable_peer(int dev_a, int dev_b);
 
 /* ---- streams / events helpers the host layer needs without torch calls ----- */
 int ddpb_stream_sync(void *stream);

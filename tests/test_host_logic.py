@@ -26,8 +26,8 @@ def test_library_exports_every_declared_symbol(native_lib):
 
 
 def test_struct_layout_matches_header():
-    # 11 pointers + 8 int32 + 5 doubles, naturally aligned
-    assert ctypes.sizeof(_lib.ToyJob) == 11 * 8 + 8 * 4 + 5 * 8
+    # 11 pointers + 8 int32 + 5 doubles + 16 peer pointers + 4 words, naturally aligned
+    assert ctypes.sizeof(_lib.ToyJob) == 11 * 8 + 8 * 4 + 5 * 8 + 16 * 8 + 16
     assert ctypes.sizeof(_lib.OptState) == 32
 
 
