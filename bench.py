@@ -255,20 +255,23 @@ def ours(args):
     cold_ms = sum(s.elapsed_time(e) for s, e in zip(starts, stops))
     cold_ms = max_over_ranks(cold_ms)
 
-    # ---- hot_l2: same steps back to back.  Single rank: straight through the C ABI (one
-    # ddpb_toy_step per iteration, the device-side counter picks the sampler row), so the
-    # host is not the bottleneck; several ranks: through the front end.
+    # ---- hot_l2: same steps back to back, straight through the C ABI as ONE captured CUDA graph
+    # of K fused launches (each node carries its sampler row; step counters live on the device),
+    # so the host is not the bottleneck.  With several ranks the gradient exchange is inside
+    # the kernel (peer windows), so the same graph works; the NCCL path goes through the front end.
     direct = None
-    if world == 1:
+    fused = world == 1 or model_X._backend.fused_exchange
+    if fused:
         eng.flush()
         n_rows = 1024
-        rows = torch.from_numpy(sampler.epochs_i32(0, n_rows // 2).reshape(n_rows, BATCH)).cuda()
+        per_epoch = len(sampler) // lb
+        rows = torch.from_numpy(sampler.epochs_i32(0, n_rows // per_epoch).reshape(n_rows, lb)).cuda()
         jobs = (_lib.ToyJob * _lib.MAX_JOBS)()
         for i, m in enumerate((model_X, model_Y)):
             j = m._backend.job
             j.loss_ring = m._backend.loss_dev.data_ptr()          # nobody reads losses in this loop: keep them in HBM
             j.x, j.y, j.idx = loader._dev[0].data_ptr(), loader._dev[1].data_ptr(), rows.data_ptr()
-            j.idx_rows, j.idx_stride, j.B, j.mode, j.n_data = n_rows, BATCH, BATCH, _lib.MODE_STEP, DATASET
+            j.idx_rows, j.idx_stride, j.B, j.mode, j.n_data = n_rows, lb, lb, _lib.MODE_STEP, DATASET
             jobs[i] = j
         stream = torch.cuda.current_stream().cuda_stream
         toy_step = _lib.lib().ddpb_toy_step
@@ -286,7 +289,7 @@ def ours(args):
             _lib.check(L.ddpb_graph_begin(cap), "ddpb_graph_begin")
             for i in range(K):
                 for k in range(2):           # every graph node carries its own sampler row: no device-side lookup
-                    jobs[k].idx, jobs[k].idx_rows = rows.data_ptr() + (i % n_rows) * BATCH * 4, 1
+                    jobs[k].idx, jobs[k].idx_rows = rows.data_ptr() + (i % n_rows) * lb * 4, 1
                 _lib.check(toy_step(jobs, 2, cap), "ddpb_toy_step")
             _lib.check(L.ddpb_graph_end(cap, ctypes.byref(graph)), "ddpb_graph_end")
             _lib.check(L.ddpb_graph_launch(graph, cap), "ddpb_graph_launch")      # warm the instantiated graph
@@ -345,7 +348,7 @@ def ours(args):
         peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
     # algorithmic bytes per launch: per model 4P (bucket) + 28P (Adam) + 48*B*H + 8*B (activations)
     alg_bytes = 2 * (4 * P + 28 * P + 48 * lb * H + 8 * lb)
-    kernel_ms = hot_ms / K if world == 1 else None
+    kernel_ms = hot_ms / K if fused else None
     achieved = alg_bytes / (kernel_ms * 1e-3) / 1e9 if kernel_ms else None
 
     cpu_baseline = None
@@ -363,10 +366,13 @@ def ours(args):
                 "config": dict(workload(world), timing="CUDA events per step; L2 flushed (256 MiB fill) between timed "
                                                        "steps; max over ranks",
                                parallelism=f"dp{world}",
+                               allreduce=("none (single rank)" if world == 1 else
+                                          "fused one-shot exchange over NVLink peer windows inside the step kernel"
+                                          if model_X._backend.fused_exchange else "ncclAllReduce per bucket + fused avg+Adam"),
                                scaling_note="one 512-sample epoch is the fixed job: 2 steps at W=1, 1 step at W>=2"),
                 "hot_l2": {"value": K * gb / (hot_ms * 1e-3), "unit": UNIT, "ms_per_step": hot_ms / K,
                            "timing": "one CUDA-event pair around K back-to-back steps, no flush"
-                                     + ("; single rank: the K launches are one captured CUDA graph" if world == 1 else "")},
+                                     + ("; the K launches are one captured CUDA graph" if fused else "")},
                 "e2e": {"value": K * gb / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms / K,
                         "h2d_bytes_per_step": lb * 12, "d2h_bytes_per_step": 8},
                 "gpu_launches": launches,
