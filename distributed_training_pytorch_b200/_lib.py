@@ -53,6 +53,7 @@ _SIGNATURES = {
     "ddpb_gather_batch": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "ddpb_toy_step": (c_int, [c_void_p, c_int, c_void_p]),
     "ddpb_toy_step_h2d": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_int64, c_void_p]),
+    "ddpb_toy_step_virtual_ranks": (c_int, [c_void_p, c_int, c_void_p]),
     "ddpb_wait_f32": (c_int, [c_void_p, ctypes.c_uint32, c_int64, c_void_p, c_void_p]),
     "ddpb_fused_avg_adam": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_float,
                                     c_double, c_double, c_double, c_double, c_int64, c_void_p]),

@@ -633,3 +633,74 @@ DDPB_API int ddpb_toy_step_h2d(const ddpb_toy_job *jobs, int njobs, void *dst_de
     }
     return launch_toy_step(jobs, njobs, (cudaStream_t)stream);
 }
+
+// ---------------------------------------------------------------------------------------
+// Several replicas of one model on ONE GPU, exchanging gradients without any allocation.
+//
+// The fused multi-rank step above needs an exchange window per rank, and somebody has to
+// allocate those.  Some callers cannot: a service that handed the whole device to another
+// memory pool at start-up (a raw cudaMalloc would fail or fragment that pool), a
+// latency-critical loop that must never take the allocator's device-wide synchronisation, a
+// test rig that wants the multi-rank arithmetic on a single-GPU box.  For them the windows
+// of up to DDPB_MAX_VIRTUAL_RANKS replicas live in the file-scope array below (96 KiB of
+// every GPU that loads this library, held until the process exits), and all replicas run in
+// one launch (blockIdx.y = replica), so they are co-resident by construction.
+//
+// Rules that follow from sharing one array:
+//   * It keeps whatever the previous call left.  The arrival flags are cleared on the stream
+//     at the start of every call (data rows are fully rewritten before they are read).
+//   * Two calls whose kernels overlap on the GPU (different streams, no dependency) race on
+//     the array; serialise them.
+//   * The device address of the array is looked up once per device, on the first call made
+//     with that device current; make that first call before any stream capture begins.
+namespace {
+
+constexpr size_t kWindowDataBytes = sizeof(float) * DDPB_XCHG_DATA_FLOATS;
+constexpr size_t kWindowFlagBytes = sizeof(uint32_t) * DDPB_XCHG_FLAG_WORDS;
+constexpr size_t kVirtualBytes = DDPB_MAX_VIRTUAL_RANKS * (kWindowDataBytes + kWindowFlagBytes);
+
+// layout: [rank 0 data][rank 1 data]...[rank 0 flags][rank 1 flags]...
+static __device__ __align__(256) unsigned char g_virtual_windows[kVirtualBytes];
+
+// In host code `g_virtual_windows` is only a handle for the runtime, never an address a kernel
+// may use: the real device address comes from cudaGetSymbolAddress, per device.
+unsigned char *g_virtual_base[64] = {};
+
+int virtual_window_base(unsigned char **base_out) {
+    int dev = -1;
+    DDPB_CUDA(cudaGetDevice(&dev));
+    DDPB_REQUIRE(dev >= 0 && dev < 64, "ddpb_toy_step_virtual_ranks: device index %d not supported", dev);
+    if (!g_virtual_base[dev]) {
+        void *ptr = nullptr;
+        DDPB_CUDA(cudaGetSymbolAddress(&ptr, g_virtual_windows));
+        g_virtual_base[dev] = static_cast<unsigned char *>(ptr);
+    }
+    *base_out = g_virtual_base[dev];
+    return 0;
+}
+
+}  // namespace
+
+DDPB_API int ddpb_toy_step_virtual_ranks(const ddpb_toy_job *jobs, int nranks, void *stream) {
+    DDPB_REQUIRE(jobs != nullptr, "ddpb_toy_step_virtual_ranks: null jobs");
+    DDPB_REQUIRE(nranks >= 2 && nranks <= DDPB_MAX_VIRTUAL_RANKS,
+                 "ddpb_toy_step_virtual_ranks: %d replicas requested, the built-in exchange windows hold 2..%d "
+                 "(use ddpb_toy_step with caller-provided windows beyond that)", nranks, DDPB_MAX_VIRTUAL_RANKS);
+    unsigned char *base = nullptr;
+    if (int rc = virtual_window_base(&base)) return rc;
+    unsigned char *flags0 = base + DDPB_MAX_VIRTUAL_RANKS * kWindowDataBytes;
+    ddpb_toy_job local[DDPB_MAX_VIRTUAL_RANKS];
+    for (int r = 0; r < nranks; ++r) {
+        DDPB_REQUIRE(jobs[r].mode == DDPB_MODE_STEP, "ddpb_toy_step_virtual_ranks: replica %d is not in STEP mode", r);
+        local[r] = jobs[r];
+        local[r].world = nranks;
+        local[r].rank = r;
+        local[r].inv_world = 1.0f / (float)nranks;
+        for (int p = 0; p < DDPB_MAX_PEERS; ++p) {
+            local[r].peer_data[p] = p < nranks ? reinterpret_cast<float *>(base + p * kWindowDataBytes) : nullptr;
+            local[r].peer_flags[p] = p < nranks ? reinterpret_cast<uint32_t *>(flags0 + p * kWindowFlagBytes) : nullptr;
+        }
+    }
+    DDPB_CUDA(cudaMemsetAsync(flags0, 0, nranks * kWindowFlagBytes, (cudaStream_t)stream));
+    return launch_toy_step(local, nranks, (cudaStream_t)stream);
+}

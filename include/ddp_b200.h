@@ -135,6 +135,22 @@ int ddpb_toy_step(const ddpb_toy_job *jobs /* host */, int njobs, void *stream);
 int ddpb_toy_step_h2d(const ddpb_toy_job *jobs, int njobs, void *dst_dev, const void *src_host,
                       int64_t bytes, void *stream);
 
+/* No counterpart in the reference.  `nranks` replicas (2..DDPB_MAX_VIRTUAL_RANKS) of one model
+ * on the CURRENT GPU take one fused data-parallel step in a single launch: jobs[r] is replica
+ * r's job (DDPB_MODE_STEP, its own params/m/v/grads/state and its own batch; all replicas'
+ * state->seq must be equal).  Unlike ddpb_toy_step with world > 1, the caller provides no
+ * exchange windows and nothing is allocated, by this call or ever: the windows are a
+ * 96 KiB array compiled into the library (every GPU that loads it holds one until exit).
+ * It is meant for callers that cannot allocate device memory themselves -- the device was
+ * handed to another pool, or the loop must not take the allocator's device-wide sync.
+ * world/rank/inv_world/peer_* of the jobs are ignored and filled in here.
+ * The array is shared by every call and keeps the previous call's contents: the arrival flags
+ * are cleared on `stream` first, and calls whose kernels overlap on the GPU race -- serialise
+ * them.  The first call on each device looks the array's device address up; make that call
+ * before starting any stream capture.  More than DDPB_MAX_VIRTUAL_RANKS replicas is an error. */
+#define DDPB_MAX_VIRTUAL_RANKS 4
+int ddpb_toy_step_virtual_ranks(const ddpb_toy_job *jobs /* host */, int nranks, void *stream);
+
 /* ---- optimizer over a flat bucket ----------------------------------------- */
 /* One pass over a (reduced) gradient bucket: g = bucket * grad_scale (the 1/W of
  * DDP's averaging, torch:distributed/algorithms/ddp_comm_hooks/default_hooks.py:24-29),
