@@ -378,7 +378,10 @@ def ours(args):
                 "gpu_launches": launches,
                 "clocks": clocks,
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                             "frac": (achieved / peak) if achieved else None, "traffic": None,
+                             "frac": (achieved / peak) if achieved else None,
+                             # dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu --set full,
+                             # profiles/r01_v3_toy_step_raw.csv (cold caches; warm launches hit L2)
+                             "traffic": 50432 if lb == BATCH else None,
                              "kernel": "toy_step_kernel", "peak_source": peak_src,
                              "algorithmic_bytes_per_launch": alg_bytes,
                              "note": "latency-bound by construction: 2 clusters x 8 CTAs, 273 KB and 1 MFLOP per launch"},

@@ -41,6 +41,15 @@ class ToyJob(ctypes.Structure):
                 ("world", c_int32), ("rank", c_int32), ("inv_world", c_float), ("reserved2", c_int32)]
 
 
+class SegJob(ctypes.Structure):
+    _fields_ = [("params", c_void_p), ("grads", c_void_p), ("m", c_void_p), ("v", c_void_p), ("state", c_void_p),
+                ("bias_table", c_void_p), ("loss_ring", c_void_p), ("x", c_void_p), ("y", c_void_p),
+                ("d_out", c_void_p), ("out", c_void_p), ("d_in", c_void_p),
+                ("B", c_int32), ("mode", c_int32), ("opt", c_int32), ("nl", c_int32), ("dims", c_int32 * 4),
+                ("act_last", c_int32), ("has_loss", c_int32), ("loss_ring_n", c_int32), ("bias_table_n", c_int32),
+                ("lr", c_double), ("beta1", c_double), ("beta2", c_double), ("eps", c_double), ("momentum", c_double)]
+
+
 _SIGNATURES = {
     "ddpb_version": (c_int, []),
     "ddpb_last_error": (c_char_p, []),
@@ -54,6 +63,7 @@ _SIGNATURES = {
     "ddpb_toy_step": (c_int, [c_void_p, c_int, c_void_p]),
     "ddpb_toy_step_h2d": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_int64, c_void_p]),
     "ddpb_toy_step_virtual_ranks": (c_int, [c_void_p, c_int, c_void_p]),
+    "ddpb_segment_step": (c_int, [c_void_p, c_void_p]),
     "ddpb_wait_f32": (c_int, [c_void_p, ctypes.c_uint32, c_int64, c_void_p, c_void_p]),
     "ddpb_fused_avg_adam": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_float,
                                     c_double, c_double, c_double, c_double, c_int64, c_void_p]),

@@ -39,7 +39,10 @@ def _required_int(name):
 
 def init_torchrun(backend, timeout=datetime.timedelta(hours=1)):
     """demo.py:25-34."""
-    dist.init_process_group(backend=backend, timeout=timeout)
+    if timeout is None:                        # demo_one_model_multi_gpu.py:49 passes no timeout
+        dist.init_process_group(backend=backend)
+    else:
+        dist.init_process_group(backend=backend, timeout=timeout)
     world_size = _required_int("WORLD_SIZE")
     local_world_size = _required_int("LOCAL_WORLD_SIZE")
     local_rank = int(os.environ["LOCAL_RANK"])

@@ -29,7 +29,7 @@ import numpy as np
 
 from .data import DeviceBatch, HostBatch, StagedBatch
 from .engine import engine_for
-from .toy_model_and_data import ToyModel
+from .toy_model_and_data import MultiGPUModel, ToyModel
 
 _OWNERS = {}          # id(nn.Parameter) -> backend
 LOSS_RING = 1024      # loss slots per model; a LossValue stays readable for this many steps
@@ -71,6 +71,12 @@ class DistributedDataParallel:
         self.device_ids = device_ids
         if isinstance(module, ToyModel) and module.hidden == _lib.TOY_HIDDEN:
             self._backend = ToyBackend(module, process_group, lazy_step)
+        elif isinstance(module, MultiGPUModel) and module.hidden == _lib.TOY_HIDDEN:
+            if device_ids is not None:
+                raise ValueError("device_ids MUST be None when the module spans several GPUs "
+                                 "(demo_one_model_multi_gpu.py:96-98)")
+            from .pipeline import PipelineBackend
+            self._backend = PipelineBackend(module, process_group, _OWNERS)
         else:
             raise NotImplementedError(
                 f"no sm_100a kernels for {type(module).__name__}"
@@ -103,6 +109,8 @@ class DistributedDataParallel:
 
     def flat_parameters(self):
         """The flat fp32 parameter vector (after everything described so far has been launched)."""
+        if hasattr(self._backend, "flat_parameters"):
+            return self._backend.flat_parameters()
         self._backend.engine.flush()
         self._backend.check_peers()
         return self._backend.params

@@ -151,6 +151,36 @@ int ddpb_toy_step_h2d(const ddpb_toy_job *jobs, int njobs, void *dst_dev, const 
 #define DDPB_MAX_VIRTUAL_RANKS 4
 int ddpb_toy_step_virtual_ranks(const ddpb_toy_job *jobs /* host */, int nranks, void *stream);
 
+/* ---- a pipeline stage of the split model ------------------------------------------- */
+/* demo_one_model_multi_gpu.py:17-42: MultiGPUModel.layers0 (2->10->10, both activated) on dev0,
+ * layers1 (10->10->10->1) on dev1, activation moved with .to(dev1) and its gradient back through
+ * autograd.  One launch runs a stage: FWD (out = stage(x)), or GRAD/STEP (forward recomputed,
+ * backward from targets `y` when has_loss, else from the upstream gradient `d_out`; parameter
+ * gradients to `grads`, optional input gradient to `d_in`, STEP also applies Adam/SGD).  `out`
+ * and `d_in` may lie in the other GPU's memory (ddpb_enable_peer): the transfer is the kernel's
+ * own stores over NVLink.  Launch with the stage's device current. */
+#define DDPB_SEG_MAX_LAYERS 3
+#define DDPB_SEG_MAX_WIDTH 10
+typedef struct ddpb_seg_job {
+    float *params, *grads;    /* flat [P], [P+1] (grads[P] = sum (o-t)^2 when has_loss) */
+    float *m, *v;
+    ddpb_opt_state *state;
+    const float *bias_table;
+    float *loss_ring;
+    const float *x;           /* [B, dims[0]] */
+    const float *y;           /* [B, dims[nl]] targets (has_loss) */
+    const float *d_out;       /* [B, dims[nl]] upstream gradient (!has_loss) */
+    float *out;               /* FWD: [B, dims[nl]] */
+    float *d_in;              /* optional [B, dims[0]] */
+    int32_t B, mode, opt, nl;
+    int32_t dims[DDPB_SEG_MAX_LAYERS + 1];
+    int32_t act_last;         /* LeakyReLU after the last layer too (stage 0) */
+    int32_t has_loss;         /* the stage ends in nn.MSELoss (demo_one_model_multi_gpu.py:107,126) */
+    int32_t loss_ring_n, bias_table_n;
+    double lr, beta1, beta2, eps, momentum;
+} ddpb_seg_job;
+int ddpb_segment_step(const ddpb_seg_job *job /* host */, void *stream);
+
 /* ---- optimizer over a flat bucket ----------------------------------------- */
 /* One pass over a (reduced) gradient bucket: g = bucket * grad_scale (the 1/W of
  * DDP's averaging, torch:distributed/algorithms/ddp_comm_hooks/default_hooks.py:24-29),

@@ -71,3 +71,22 @@ def test_standard_dataloader_mode(tmp_path):
     ranks = _run_demo(tmp_path, 2, "p2p", ("--backend=nccl", "--torchrun", "--dry_run", "--dataloader=standard"))
     assert np.array_equal(ranks[0]["px"], ranks[1]["px"])
     assert np.isfinite(ranks[0]["losses"]).all() and ranks[0]["losses"][-1, 0] < ranks[0]["losses"][0, 0]
+
+
+def test_mpiexec_entry_point_with_the_compat_launcher(tmp_path, golden_dir):
+    """demo_assume_started_with_mpiexec.py started by tools/mpiexec_compat.py (no MPI in the image):
+    the logged values are each rank's LOCAL loss (the reference reduces temporaries), the model
+    trajectory is the same as demo.py's."""
+    world = 2 if 2 in _worlds() else 1
+    env = dict(os.environ, DDPB_ITERATIONS="200", DDPB_SEED="1234", DDPB_TEST_ENTRY="mpiexec", OMP_NUM_THREADS="1",
+               TASKS_PER_NODE=str(world))
+    cmd = [sys.executable, os.path.join(ROOT, "tools", "mpiexec_compat.py"), "-n", str(world), sys.executable,
+           os.path.join(ROOT, "tests", "_demo_worker.py"), str(tmp_path), "--backend=nccl"]
+    proc = subprocess.run(cmd, env=env, cwd=ROOT, capture_output=True, text=True, timeout=600)
+    assert proc.returncode == 0, (proc.stdout + proc.stderr)[-4000:]
+    g = np.load(os.path.join(golden_dir, f"ref_w{world}.npz"))
+    ranks = [np.load(os.path.join(tmp_path, f"rank{r}.npz")) for r in range(world)]
+    assert np.max(np.abs(ranks[0]["px"] - g["mid_X"])) <= 2e-5 and np.max(np.abs(ranks[0]["py"] - g["mid_Y"])) <= 2e-5
+    mean = np.mean([r["losses"] for r in ranks], axis=0)          # equal shards: mean of local losses = logged value
+    ref = np.stack([g["lossX"], g["lossY"]], axis=1)[:200]
+    assert np.max(np.abs(mean - ref) / ref) <= 2e-5
