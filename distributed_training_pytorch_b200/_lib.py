@@ -63,6 +63,9 @@ _SIGNATURES = {
     "ddpb_toy_step": (c_int, [c_void_p, c_int, c_void_p]),
     "ddpb_toy_step_h2d": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_int64, c_void_p]),
     "ddpb_toy_step_virtual_ranks": (c_int, [c_void_p, c_int, c_void_p]),
+    "ddpb_linear_fwd": (c_int, [c_void_p] * 5 + [c_int] * 5 + [c_void_p]),
+    "ddpb_linear_dgrad": (c_int, [c_void_p] * 5 + [c_int] * 4 + [c_void_p]),
+    "ddpb_linear_wgrad": (c_int, [c_void_p] * 4 + [c_int] * 4 + [c_void_p]),
     "ddpb_segment_step": (c_int, [c_void_p, c_void_p]),
     "ddpb_wait_f32": (c_int, [c_void_p, ctypes.c_uint32, c_int64, c_void_p, c_void_p]),
     "ddpb_fused_avg_adam": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_float,

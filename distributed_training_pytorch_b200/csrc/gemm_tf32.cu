@@ -1,0 +1,353 @@
+// Tiled tensor-core GEMMs for the WIDENED toy model (hidden width H a multiple of 128,
+// BASELINE.json configs[4]): the three H x H linear layers run forward, dgrad and wgrad as
+// tcgen05 (5th-generation tensor core) kind::tf32 MMAs fed by TMA.
+//
+// Reference: the same nn.Linear layers (toy_model_and_data.py:13-21, widths scaled up) that
+// PyTorch runs as cuBLAS sgemm calls in forward and in autograd's backward (demo.py:104-109).
+//
+//   D[m][n] = sum_k A(m,k) * B(n,k)          one 128 x 128 output tile per CTA
+//
+//   forward   m = sample, n = output neuron, k = input neuron   A = act_in [B,Hin]   K-major
+//                                                                B = W [Hout,Hin]      K-major
+//             epilogue: + bias, LeakyReLU, store act_out [B,Hout] and its transpose [Hout,ld]
+//   dgrad     m = sample, n = input neuron,  k = output neuron   A = dZ [B,Hout]      K-major
+//                                                                B = W [Hout,Hin]      MN-major (n contiguous)
+//             epilogue: x LeakyReLU'(act_prev), store dZ_prev [B,Hin] and its transpose
+//   wgrad     m = output neuron, n = input neuron, k = sample    A = dZ^T [Hout,ld]    K-major
+//                                                                B = act^T [Hin+..,ld] K-major
+//             epilogue: store dW straight into the flat gradient bucket; the operand row
+//             n = Hin is a row of ones, which makes column Hin of the product the bias gradient
+//
+// Structure (one CTA, 256 threads): warp 0 = TMA producer, warp 1 = MMA issuer (one elected
+// thread), warp 2 = TMEM allocator, warps 4..7 = epilogue (tcgen05.ld 32 lanes x 32 columns at a
+// time).  A 6-stage ring of {A tile, B tile} (32 KB per stage, 128-byte swizzle) is filled by
+// cp.async.bulk.tensor with mbarrier complete_tx and drained by tcgen05.commit.
+// Operands are fp32 in HBM and shared memory; the tensor core reads them as tf32 (10-bit
+// mantissa) and accumulates in fp32 in TMEM -- the tolerance of this path is stated in
+// tests/test_gpu_wide.py.  These GEMMs sit at the HBM/tensor ridge for B <= 256 (each weight byte
+// feeds 128 FLOP per pass): the roofline is weight bytes / HBM bandwidth.
+#include "common.cuh"
+#include <cuda.h>
+
+namespace {
+
+constexpr int BM = 128, BN = 128, BK = 32;           // BK tf32 = 128 bytes = one swizzle atom row
+constexpr int kStages = 6;
+constexpr int kThreads = 256;
+constexpr int kTileBytes = BM * BK * 4;              // 16 KB per operand tile
+constexpr int kStageBytes = 2 * kTileBytes;
+constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*alignment slack*/ + 256 /*barriers*/;
+constexpr int kTmemCols = BN;                        // fp32 accumulator: 128 lanes x 128 columns
+constexpr float kSlope = 0.01f;
+
+enum { EPI_FWD = 0, EPI_DGRAD = 1, EPI_WGRAD = 2 };
+
+struct EpiParams {
+    const float *bias;        // FWD: [N]
+    const float *act_prev;    // DGRAD: [M, ld_out] activation whose sign is the LeakyReLU mask
+    float *out;               // FWD: act_out [M, ld_out]; DGRAD: dZ_prev [M, ld_out]; WGRAD: dW [M, ld_out]
+    float *out_t;             // FWD / DGRAD: transposed copy [N, ld_t]; WGRAD: bias gradient [M]
+    int ld_out, ld_t;
+    int apply_act;            // FWD: LeakyReLU after the bias
+    int n_real;               // WGRAD: Hin (column n_real of the product is the bias gradient)
+};
+
+// ---- PTX wrappers ---------------------------------------------------------------------------
+__device__ __forceinline__ unsigned saddr(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
+    unsigned done;
+    do {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+    } while (!done);
+}
+__device__ __forceinline__ void tma_load_2d(unsigned dst, const CUtensorMap *map, unsigned bar, int c0, int c1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tmem_alloc(unsigned slot_smem, unsigned cols) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(slot_smem), "r"(cols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(unsigned taddr, unsigned cols) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
+}
+__device__ __forceinline__ void umma_tf32(unsigned tmem_d, unsigned long long desc_a, unsigned long long desc_b,
+                                          unsigned idesc, unsigned accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit(unsigned bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(unsigned taddr, float (&v)[32]) {
+    unsigned r[32];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+          "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+          "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr) : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+// Shared-memory matrix descriptor (tcgen05), 128-byte swizzle.
+//   K-major tile  [rows][32 tf32]: rows 128 B apart, 8-row groups 1024 B apart (SBO); LBO unused.
+//   MN-major tile [32 k][32 n] boxes of 4 KB: 8-k groups 1024 B apart (SBO), 32-wide n atoms 4096 B apart (LBO).
+__device__ __forceinline__ unsigned long long make_desc(unsigned smem_byte_addr, unsigned lbo_bytes, unsigned sbo_bytes) {
+    unsigned long long d = 0;
+    d |= (unsigned long long)((smem_byte_addr & 0x3FFFFu) >> 4);
+    d |= (unsigned long long)(lbo_bytes >> 4) << 16;
+    d |= (unsigned long long)(sbo_bytes >> 4) << 32;
+    d |= 1ull << 46;                       // descriptor version (Blackwell)
+    d |= 2ull << 61;                       // SWIZZLE_128B
+    return d;
+}
+
+// Instruction descriptor: fp32 accumulate, tf32 x tf32, M = 128, N = BN.
+__device__ __forceinline__ unsigned make_idesc(bool b_mn_major) {
+    unsigned d = 0;
+    d |= 1u << 4;                          // D format F32
+    d |= 2u << 7;                          // A format TF32
+    d |= 2u << 10;                         // B format TF32
+    d |= (b_mn_major ? 1u : 0u) << 16;     // B major: 0 = K, 1 = MN
+    d |= (unsigned)(BN >> 3) << 17;
+    d |= (unsigned)(BM >> 4) << 24;
+    return d;
+}
+
+template <int EPI, bool B_MN>
+__global__ void __launch_bounds__(kThreads, 1)
+gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                 const EpiParams ep, int M, int N, int K) {
+    extern __shared__ unsigned char smem_raw[];
+    // 1024-byte alignment for the swizzle atoms
+    unsigned char *smem = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    unsigned long long *bars = reinterpret_cast<unsigned long long *>(smem + kStages * kStageBytes);
+    // bars[0..S) full, bars[S..2S) empty, bars[2S] accumulator ready, then the TMEM address slot
+    unsigned *tmem_slot = reinterpret_cast<unsigned *>(bars + 2 * kStages + 1);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int n0 = blockIdx.x * BN, m0 = blockIdx.y * BM;
+    const int num_k = (K + BK - 1) / BK;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kStages; ++s) {
+            mbar_init(saddr(&bars[s]), 1);
+            mbar_init(saddr(&bars[kStages + s]), 1);
+        }
+        mbar_init(saddr(&bars[2 * kStages]), 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
+    }
+    if (warp == 2) tmem_alloc(saddr(tmem_slot), kTmemCols);
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const unsigned tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===== TMA producer =====
+        if (lane == 0) {
+            for (int kb = 0; kb < num_k; ++kb) {
+                const int s = kb % kStages;
+                if (kb >= kStages) mbar_wait(saddr(&bars[kStages + s]), ((kb / kStages) - 1) & 1);
+                const unsigned full = saddr(&bars[s]);
+                const unsigned a_dst = saddr(smem + s * kStageBytes), b_dst = a_dst + kTileBytes;
+                mbar_expect_tx(full, kStageBytes);
+                tma_load_2d(a_dst, &map_a, full, kb * BK, m0);                       // [128 rows][32 k]
+                if (!B_MN) {
+                    tma_load_2d(b_dst, &map_b, full, kb * BK, n0);                   // [128 rows][32 k]
+                } else {
+#pragma unroll
+                    for (int a = 0; a < BN / 32; ++a)                                // 4 boxes [32 k][32 n]
+                        tma_load_2d(b_dst + a * 4096, &map_b, full, n0 + a * 32, kb * BK);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer (one thread) =====
+        if (lane == 0) {
+            const unsigned idesc = make_idesc(B_MN);
+            for (int kb = 0; kb < num_k; ++kb) {
+                const int s = kb % kStages;
+                mbar_wait(saddr(&bars[s]), (kb / kStages) & 1);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const unsigned a_base = saddr(smem + s * kStageBytes), b_base = a_base + kTileBytes;
+#pragma unroll
+                for (int k = 0; k < BK / 8; ++k) {                                   // UMMA_K = 8 for tf32
+                    const unsigned long long da = make_desc(a_base + k * 32, 0, 1024);
+                    const unsigned long long db = B_MN ? make_desc(b_base + k * 1024, 4096, 1024)
+                                                       : make_desc(b_base + k * 32, 0, 1024);
+                    umma_tf32(tmem_base, da, db, idesc, (kb | k) != 0);
+                }
+                umma_commit(saddr(&bars[kStages + s]));                              // frees the stage when the MMAs retire
+            }
+            umma_commit(saddr(&bars[2 * kStages]));                                  // accumulator complete
+        }
+    } else if (warp >= 4) {
+        // ===== epilogue: TMEM -> registers -> global =====
+        const int q = warp - 4;                                                      // TMEM lanes [32q, 32q+32)
+        const int m = m0 + q * 32 + lane;
+        mbar_wait(saddr(&bars[2 * kStages]), 0);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+#pragma unroll 1
+        for (int c0 = 0; c0 < BN; c0 += 32) {
+            float v[32];
+            tmem_ld32(tmem_base + ((unsigned)(q * 32) << 16) + (unsigned)c0, v);
+            const int nb = n0 + c0;
+            if (EPI == EPI_FWD) {
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                    float z = v[i] + ((nb + i < N) ? __ldg(ep.bias + nb + i) : 0.f);
+                    v[i] = ep.apply_act ? (z > 0.f ? z : z * kSlope) : z;
+                }
+            } else if (EPI == EPI_DGRAD) {
+                if (m < M) {
+                    const float4 *ap = reinterpret_cast<const float4 *>(ep.act_prev + (size_t)m * ep.ld_out + nb);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const float4 a = (nb + 4 * i < N) ? __ldg(ap + i) : make_float4(1.f, 1.f, 1.f, 1.f);
+                        v[4 * i + 0] = a.x > 0.f ? v[4 * i + 0] : v[4 * i + 0] * kSlope;
+                        v[4 * i + 1] = a.y > 0.f ? v[4 * i + 1] : v[4 * i + 1] * kSlope;
+                        v[4 * i + 2] = a.z > 0.f ? v[4 * i + 2] : v[4 * i + 2] * kSlope;
+                        v[4 * i + 3] = a.w > 0.f ? v[4 * i + 3] : v[4 * i + 3] * kSlope;
+                    }
+                }
+            }
+            if (EPI == EPI_WGRAD) {
+                if (m < M) {
+                    if (nb < ep.n_real) {                                            // dW rows, 128 B per thread and chunk
+                        float4 *op = reinterpret_cast<float4 *>(ep.out + (size_t)m * ep.ld_out + nb);
+#pragma unroll
+                        for (int i = 0; i < 8; ++i)
+                            if (nb + 4 * i < ep.n_real) op[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+                    } else if (nb == ep.n_real) {
+                        ep.out_t[m] = v[0];                                          // product with the row of ones
+                    }
+                }
+            } else {
+                if (m < M) {
+                    float4 *op = reinterpret_cast<float4 *>(ep.out + (size_t)m * ep.ld_out + nb);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i)
+                        if (nb + 4 * i < N) op[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+                }
+                if (ep.out_t) {                                                      // transposed copy: lanes = consecutive m
+#pragma unroll
+                    for (int i = 0; i < 32; ++i)
+                        if (nb + i < N && m < M) ep.out_t[(size_t)(nb + i) * ep.ld_t + m] = v[i];
+                }
+            }
+        }
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    }
+    __syncthreads();
+    if (warp == 2) {
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        tmem_dealloc(tmem_base, kTmemCols);
+    }
+}
+
+// ---- host side ------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_tiled() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+    }
+    return fn;
+}
+
+// 2-D fp32 tensor [rows][cols] with row pitch ld (elements); box = [box_rows][box_cols], 128B swizzle.
+int make_map(CUtensorMap *map, const float *base, long long rows, long long cols, long long ld, int box_rows, int box_cols) {
+    EncodeTiledFn enc = encode_tiled();
+    if (!enc) return ddpb::fail(5, "cuTensorMapEncodeTiled is not available from this driver");
+    DDPB_REQUIRE(((uintptr_t)base & 15) == 0 && (ld * 4) % 16 == 0, "TMA operand must be 16-byte aligned with a 16-byte row pitch");
+    const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    const cuuint64_t strides[1] = {(cuuint64_t)ld * 4};
+    const cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
+    const cuuint32_t estr[2] = {1, 1};
+    CUresult rc = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float *>(base), dims, strides, box, estr,
+                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (rc != CUDA_SUCCESS) return ddpb::fail(3000 + (int)rc, "cuTensorMapEncodeTiled failed (CUresult %d)", (int)rc);
+    return 0;
+}
+
+template <int EPI, bool B_MN>
+int launch(const CUtensorMap &ma, const CUtensorMap &mb, const EpiParams &ep, int M, int N, int K, cudaStream_t stream) {
+    static bool configured = false;
+    if (!configured) {
+        DDPB_CUDA(cudaFuncSetAttribute(gemm_tf32_kernel<EPI, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+        configured = true;
+    }
+    dim3 grid((N + BN - 1) / BN, (M + BM - 1) / BM, 1);
+    gemm_tf32_kernel<EPI, B_MN><<<grid, kThreads, kSmemBytes, stream>>>(ma, mb, ep, M, N, K);
+    DDPB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+}  // namespace
+
+DDPB_API int ddpb_linear_fwd(const float *act_in, const float *W, const float *bias, float *act_out, float *act_out_t,
+                             int B, int Hin, int Hout, int ld_t, int apply_act, void *stream) {
+    DDPB_REQUIRE(act_in && W && bias && act_out && B >= 1 && Hin >= 32 && Hout >= 32 && Hin % 4 == 0 && Hout % 4 == 0,
+                 "ddpb_linear_fwd: bad arguments (B=%d Hin=%d Hout=%d)", B, Hin, Hout);
+    DDPB_REQUIRE(!act_out_t || ld_t >= B, "ddpb_linear_fwd: transposed pitch %d < batch %d", ld_t, B);
+    CUtensorMap ma, mb;
+    if (int rc = make_map(&ma, act_in, B, Hin, Hin, BM, BK)) return rc;
+    if (int rc = make_map(&mb, W, Hout, Hin, Hin, BN, BK)) return rc;
+    EpiParams ep = {bias, nullptr, act_out, act_out_t, Hout, ld_t, apply_act, 0};
+    return launch<EPI_FWD, false>(ma, mb, ep, B, Hout, Hin, (cudaStream_t)stream);
+}
+
+DDPB_API int ddpb_linear_dgrad(const float *dz, const float *W, const float *act_prev, float *dz_prev, float *dz_prev_t,
+                               int B, int Hin, int Hout, int ld_t, void *stream) {
+    DDPB_REQUIRE(dz && W && act_prev && dz_prev && B >= 1 && Hin >= 32 && Hout >= 32 && Hin % 4 == 0 && Hout % 4 == 0,
+                 "ddpb_linear_dgrad: bad arguments (B=%d Hin=%d Hout=%d)", B, Hin, Hout);
+    DDPB_REQUIRE(!dz_prev_t || ld_t >= B, "ddpb_linear_dgrad: transposed pitch %d < batch %d", ld_t, B);
+    CUtensorMap ma, mb;
+    if (int rc = make_map(&ma, dz, B, Hout, Hout, BM, BK)) return rc;                 // A: [m = sample][k = out neuron]
+    if (int rc = make_map(&mb, W, Hout, Hin, Hin, BK, 32)) return rc;                 // B: boxes [32 k][32 n], n contiguous
+    EpiParams ep = {nullptr, act_prev, dz_prev, dz_prev_t, Hin, ld_t, 0, 0};
+    return launch<EPI_DGRAD, true>(ma, mb, ep, B, Hin, Hout, (cudaStream_t)stream);
+}
+
+DDPB_API int ddpb_linear_wgrad(const float *dz_t, const float *act_t_ext, float *dW, float *db, int B, int Hin, int Hout,
+                               int ld_t, void *stream) {
+    DDPB_REQUIRE(dz_t && act_t_ext && dW && db && B >= 1 && Hin >= 32 && Hout >= 32 && Hin % 4 == 0 && ld_t % 4 == 0 && ld_t >= B,
+                 "ddpb_linear_wgrad: bad arguments (B=%d Hin=%d Hout=%d ld_t=%d)", B, Hin, Hout, ld_t);
+    CUtensorMap ma, mb;
+    if (int rc = make_map(&ma, dz_t, Hout, B, ld_t, BM, BK)) return rc;               // A: [m = out neuron][k = sample]
+    if (int rc = make_map(&mb, act_t_ext, Hin + 1, B, ld_t, BN, BK)) return rc;       // B: [n = in neuron | ones][k = sample]
+    EpiParams ep = {nullptr, nullptr, dW, db, Hin, 0, 0, Hin};
+    return launch<EPI_WGRAD, false>(ma, mb, ep, Hout, Hin + 1, B, (cudaStream_t)stream);
+}

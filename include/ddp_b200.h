@@ -181,6 +181,23 @@ typedef struct ddpb_seg_job {
 } ddpb_seg_job;
 int ddpb_segment_step(const ddpb_seg_job *job /* host */, void *stream);
 
+/* ---- widened model: tensor-core linear layers (hidden width a multiple of 4, >= 32) ---- */
+/* The H x H nn.Linear layers of the widened toy model (toy_model_and_data.py:13-21 with the
+ * widths scaled up, BASELINE.json configs[4]) as tcgen05 kind::tf32 GEMMs fed by TMA; PyTorch
+ * runs them as cuBLAS sgemm in forward and in autograd (demo.py:104-109).  fp32 storage, tf32
+ * multiplication, fp32 accumulation.  B = local batch.  Transposed copies ([H, ld_t], ld_t >= B,
+ * ld_t % 4 == 0) are written by the producing epilogues so that every wgrad operand is K-major.
+ *   fwd:   act_out[B,Hout] = act(act_in[B,Hin] W^T + bias); act_out_t (optional) = its transpose
+ *   dgrad: dz_prev[B,Hin] = (dz[B,Hout] W) * LeakyReLU'(act_prev); dz_prev_t = its transpose
+ *   wgrad: dW[Hout,Hin] = dz_t[Hout,:B] act_t_ext[:Hin,:B]^T; db[Hout] = dz_t . ones, where
+ *          act_t_ext has Hin+1 rows and row Hin is all ones */
+int ddpb_linear_fwd(const float *act_in, const float *W, const float *bias, float *act_out, float *act_out_t,
+                    int B, int Hin, int Hout, int ld_t, int apply_act, void *stream);
+int ddpb_linear_dgrad(const float *dz, const float *W, const float *act_prev, float *dz_prev, float *dz_prev_t,
+                      int B, int Hin, int Hout, int ld_t, void *stream);
+int ddpb_linear_wgrad(const float *dz_t, const float *act_t_ext, float *dW, float *db, int B, int Hin, int Hout,
+                      int ld_t, void *stream);
+
 /* ---- optimizer over a flat bucket ----------------------------------------- */
 /* One pass over a (reduced) gradient bucket: g = bucket * grad_scale (the 1/W of
  * DDP's averaging, torch:distributed/algorithms/ddp_comm_hooks/default_hooks.py:24-29),

@@ -1,0 +1,86 @@
+"""Widened model (BASELINE.json configs[4]): the tcgen05/TMA tf32 linear-layer GEMMs through the
+C ABI against an fp32 PyTorch reference of the same op (a floating-point kernel, so the
+reference is torch fp32 with TF32 disabled).
+
+Tolerance: operands are truncated to tf32 (10 explicit mantissa bits, relative error <= 2^-10
+per operand) and accumulated in fp32, so an inner product of length K with terms of magnitude
+|a||b| errs by about 2^-10 * sqrt(K) * rms(|a||b|); the tests allow 4e-3 of the output's max
+magnitude (measured: ~5e-4)."""
+import numpy as np
+import pytest
+import torch
+
+from distributed_training_pytorch_b200 import _lib
+
+pytestmark = pytest.mark.gpu
+
+TOL = 4e-3
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _close(got, ref):
+    scale = ref.abs().max().item()
+    err = (got - ref).abs().max().item()
+    assert err <= TOL * scale, (err, scale)
+    return err / scale
+
+
+@pytest.fixture(autouse=True)
+def _fp32_reference():
+    torch.backends.cuda.matmul.allow_tf32 = False
+    yield
+
+
+@pytest.mark.parametrize("B,Hin,Hout", [(256, 256, 256), (64, 512, 384), (128, 1024, 1024), (100, 384, 640), (256, 2048, 2048)])
+def test_linear_fwd(native_lib, B, Hin, Hout):
+    g = torch.Generator(device="cuda").manual_seed(B + Hin)
+    x = torch.randn(B, Hin, device="cuda", generator=g)
+    W = torch.randn(Hout, Hin, device="cuda", generator=g) / Hin ** 0.5
+    b = torch.randn(Hout, device="cuda", generator=g)
+    ld = (B + 3) // 4 * 4
+    out, out_t = torch.full((B, Hout), float("nan"), device="cuda"), torch.full((Hout, ld), float("nan"), device="cuda")
+    _lib.check(native_lib.ddpb_linear_fwd(x.data_ptr(), W.data_ptr(), b.data_ptr(), out.data_ptr(), out_t.data_ptr(),
+                                          B, Hin, Hout, ld, 1, _stream()))
+    ref = torch.nn.functional.leaky_relu(x @ W.t() + b, 0.01)
+    _close(out, ref)
+    assert torch.equal(out_t[:, :B], out.t())
+    _lib.check(native_lib.ddpb_linear_fwd(x.data_ptr(), W.data_ptr(), b.data_ptr(), out.data_ptr(), None,
+                                          B, Hin, Hout, ld, 0, _stream()))
+    _close(out, x @ W.t() + b)
+
+
+@pytest.mark.parametrize("B,Hin,Hout", [(256, 256, 256), (64, 512, 384), (128, 1024, 1024), (100, 384, 640)])
+def test_linear_dgrad(native_lib, B, Hin, Hout):
+    g = torch.Generator(device="cuda").manual_seed(B + Hout)
+    dz = torch.randn(B, Hout, device="cuda", generator=g)
+    W = torch.randn(Hout, Hin, device="cuda", generator=g) / Hout ** 0.5
+    act_prev = torch.nn.functional.leaky_relu(torch.randn(B, Hin, device="cuda", generator=g), 0.01)
+    ld = (B + 3) // 4 * 4
+    out, out_t = torch.full((B, Hin), float("nan"), device="cuda"), torch.full((Hin, ld), float("nan"), device="cuda")
+    _lib.check(native_lib.ddpb_linear_dgrad(dz.data_ptr(), W.data_ptr(), act_prev.data_ptr(), out.data_ptr(),
+                                            out_t.data_ptr(), B, Hin, Hout, ld, _stream()))
+    ref = (dz @ W) * torch.where(act_prev > 0, 1.0, 0.01)
+    _close(out, ref)
+    assert torch.equal(out_t[:, :B], out.t())
+
+
+@pytest.mark.parametrize("B,Hin,Hout", [(256, 256, 256), (64, 512, 384), (128, 1024, 1024), (100, 384, 640)])
+def test_linear_wgrad(native_lib, B, Hin, Hout):
+    g = torch.Generator(device="cuda").manual_seed(B * 3 + Hout)
+    ld = (B + 3) // 4 * 4
+    dz_t = torch.zeros(Hout, ld, device="cuda")
+    dz_t[:, :B] = torch.randn(Hout, B, device="cuda", generator=g)
+    act_t = torch.zeros(Hin + 1, ld, device="cuda")
+    act_t[:Hin, :B] = torch.randn(Hin, B, device="cuda", generator=g)
+    act_t[Hin, :B] = 1.0
+    if ld > B:                       # pitch padding must not leak into the product (TMA bounds = B)
+        dz_t[:, B:] = 7.0
+        act_t[:, B:] = 7.0
+    dW, db = torch.full((Hout, Hin), float("nan"), device="cuda"), torch.full((Hout,), float("nan"), device="cuda")
+    _lib.check(native_lib.ddpb_linear_wgrad(dz_t.data_ptr(), act_t.data_ptr(), dW.data_ptr(), db.data_ptr(), B, Hin, Hout,
+                                            ld, _stream()))
+    _close(dW, dz_t[:, :B] @ act_t[:Hin, :B].t())
+    _close(db, dz_t[:, :B].sum(dim=1))
