@@ -110,16 +110,21 @@ __device__ __forceinline__ void tmem_ld32(unsigned taddr, float (&v)[32]) {
     for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
 }
 
-// Shared-memory matrix descriptor (tcgen05), 128-byte swizzle.
-//   K-major tile  [rows][32 tf32]: rows 128 B apart, 8-row groups 1024 B apart (SBO); LBO unused.
-//   MN-major tile [32 k][32 n] boxes of 4 KB: 8-k groups 1024 B apart (SBO), 32-wide n atoms 4096 B apart (LBO).
-__device__ __forceinline__ unsigned long long make_desc(unsigned smem_byte_addr, unsigned lbo_bytes, unsigned sbo_bytes) {
+// Shared-memory matrix descriptor (tcgen05).
+//   K-major tile  [rows][32 tf32], SWIZZLE_128B (type 2): rows 128 B apart, 8-row groups 1024 B
+//     apart (SBO); LBO unused.
+//   MN-major tile of 32-bit elements: the only legal layout is "128B swizzle with 32B atoms"
+//     (type 1, TMA CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B): boxes [32 k][32 n] of 4 KB, k rows 128 B
+//     apart, 4-row k groups 512 B apart (SBO), 32-wide n atoms 4096 B apart (LBO).  (Plain
+//     SWIZZLE_128B on an MN-major tf32 operand silently multiplies by zero -- measured.)
+__device__ __forceinline__ unsigned long long make_desc(unsigned smem_byte_addr, unsigned lbo_bytes, unsigned sbo_bytes,
+                                                        unsigned layout_type) {
     unsigned long long d = 0;
     d |= (unsigned long long)((smem_byte_addr & 0x3FFFFu) >> 4);
     d |= (unsigned long long)(lbo_bytes >> 4) << 16;
     d |= (unsigned long long)(sbo_bytes >> 4) << 32;
     d |= 1ull << 46;                       // descriptor version (Blackwell)
-    d |= 2ull << 61;                       // SWIZZLE_128B
+    d |= (unsigned long long)layout_type << 61;
     return d;
 }
 
@@ -196,9 +201,9 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
                 const unsigned a_base = saddr(smem + s * kStageBytes), b_base = a_base + kTileBytes;
 #pragma unroll
                 for (int k = 0; k < BK / 8; ++k) {                                   // UMMA_K = 8 for tf32
-                    const unsigned long long da = make_desc(a_base + k * 32, 0, 1024);
-                    const unsigned long long db = B_MN ? make_desc(b_base + k * 1024, 4096, 1024)
-                                                       : make_desc(b_base + k * 32, 0, 1024);
+                    const unsigned long long da = make_desc(a_base + k * 32, 0, 1024, 2);
+                    const unsigned long long db = B_MN ? make_desc(b_base + k * 1024, 4096, 512, 1)
+                                                       : make_desc(b_base + k * 32, 0, 1024, 2);
                     umma_tf32(tmem_base, da, db, idesc, (kb | k) != 0);
                 }
                 umma_commit(saddr(&bars[kStages + s]));                              // frees the stage when the MMAs retire
@@ -287,7 +292,8 @@ EncodeTiledFn encode_tiled() {
 }
 
 // 2-D fp32 tensor [rows][cols] with row pitch ld (elements); box = [box_rows][box_cols], 128B swizzle.
-int make_map(CUtensorMap *map, const float *base, long long rows, long long cols, long long ld, int box_rows, int box_cols) {
+int make_map(CUtensorMap *map, const float *base, long long rows, long long cols, long long ld, int box_rows, int box_cols,
+             CUtensorMapSwizzle swizzle = CU_TENSOR_MAP_SWIZZLE_128B) {
     EncodeTiledFn enc = encode_tiled();
     if (!enc) return ddpb::fail(5, "cuTensorMapEncodeTiled is not available from this driver");
     DDPB_REQUIRE(((uintptr_t)base & 15) == 0 && (ld * 4) % 16 == 0, "TMA operand must be 16-byte aligned with a 16-byte row pitch");
@@ -296,7 +302,7 @@ int make_map(CUtensorMap *map, const float *base, long long rows, long long cols
     const cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
     const cuuint32_t estr[2] = {1, 1};
     CUresult rc = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float *>(base), dims, strides, box, estr,
-                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                      CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                       CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (rc != CUDA_SUCCESS) return ddpb::fail(3000 + (int)rc, "cuTensorMapEncodeTiled failed (CUresult %d)", (int)rc);
     return 0;
@@ -336,7 +342,7 @@ DDPB_API int ddpb_linear_dgrad(const float *dz, const float *W, const float *act
     DDPB_REQUIRE(!dz_prev_t || ld_t >= B, "ddpb_linear_dgrad: transposed pitch %d < batch %d", ld_t, B);
     CUtensorMap ma, mb;
     if (int rc = make_map(&ma, dz, B, Hout, Hout, BM, BK)) return rc;                 // A: [m = sample][k = out neuron]
-    if (int rc = make_map(&mb, W, Hout, Hin, Hin, BK, 32)) return rc;                 // B: boxes [32 k][32 n], n contiguous
+    if (int rc = make_map(&mb, W, Hout, Hin, Hin, BK, 32, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B)) return rc;   // B: boxes [32 k][32 n], n contiguous
     EpiParams ep = {nullptr, act_prev, dz_prev, dz_prev_t, Hin, ld_t, 0, 0};
     return launch<EPI_DGRAD, true>(ma, mb, ep, B, Hin, Hout, (cudaStream_t)stream);
 }
