@@ -66,6 +66,10 @@ _SIGNATURES = {
     "ddpb_linear_fwd": (c_int, [c_void_p] * 5 + [c_int] * 5 + [c_void_p]),
     "ddpb_linear_dgrad": (c_int, [c_void_p] * 5 + [c_int] * 4 + [c_void_p]),
     "ddpb_linear_wgrad": (c_int, [c_void_p] * 4 + [c_int] * 4 + [c_void_p]),
+    "ddpb_wide_first_fwd": (c_int, [c_void_p] * 6 + [c_int] * 3 + [c_void_p]),
+    "ddpb_wide_last_fwd": (c_int, [c_void_p] * 8 + [c_int] * 2 + [c_void_p]),
+    "ddpb_wide_last_bwd": (c_int, [c_void_p] * 10 + [c_int] * 3 + [c_void_p]),
+    "ddpb_wide_first_bwd": (c_int, [c_void_p] * 5 + [c_int] * 2 + [c_void_p]),
     "ddpb_segment_step": (c_int, [c_void_p, c_void_p]),
     "ddpb_wait_f32": (c_int, [c_void_p, ctypes.c_uint32, c_int64, c_void_p, c_void_p]),
     "ddpb_fused_avg_adam": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_float,

@@ -71,6 +71,9 @@ class DistributedDataParallel:
         self.device_ids = device_ids
         if isinstance(module, ToyModel) and module.hidden == _lib.TOY_HIDDEN:
             self._backend = ToyBackend(module, process_group, lazy_step)
+        elif isinstance(module, ToyModel):
+            from .wide import WideBackend
+            self._backend = WideBackend(module, process_group, bucket_cap_mb, _OWNERS)
         elif isinstance(module, MultiGPUModel) and module.hidden == _lib.TOY_HIDDEN:
             if device_ids is not None:
                 raise ValueError("device_ids MUST be None when the module spans several GPUs "

@@ -1,0 +1,296 @@
+"""Widened toy model (hidden width H, BASELINE.json configs[4]) behind the same wrapper.
+
+The reference has no width knob (toy_model_and_data.py:13-21 are literals); ToyModel(hidden=H) /
+DDPB_HIDDEN is the additive one.  With H in the thousands the step is no longer latency-bound:
+the three H x H layers are tcgen05/TMA tf32 GEMMs (csrc/gemm_tf32.cu), the thin ends are
+streaming kernels (csrc/wide_edges.cu), weight gradients are written straight into the flat
+bucket, and the optimizer is the fused average+Adam pass (28 B/param).  With several ranks the
+flat gradient is cut into buckets (bucket_cap_mb, reverse parameter order like the c10d reducer,
+torch:nn/parallel/distributed.py:1255-1283); each bucket's ncclAllReduce and its Adam pass run on
+a communication stream as soon as the kernels that produce the bucket have been issued, i.e.
+overlapped with the rest of backward (demo.py:107-111 -> reducer hooks + optimizer.step()).
+"""
+import ctypes
+import os
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from . import _lib
+from .data import DeviceBatch, HostBatch, StagedBatch
+from .engine import engine_for
+
+LOSS_RING = 1024
+LOSS_SENTINEL = 0x7FC0DEAD
+CAP_B = 256          # local batch capacity of the work buffers (the reference's batch_size, demo.py:145)
+
+
+class WideBackend:
+    def __init__(self, module, process_group, bucket_cap_mb, owners):
+        tensors = list(module.parameters())
+        dev = tensors[0].device
+        if dev.type != "cuda" or any(p.device != dev for p in tensors):
+            raise _lib.DdpB200Error("DistributedDataParallel needs the module on ONE CUDA device; there is no CPU path")
+        H = module.hidden
+        if H < 32 or H % 32:
+            raise NotImplementedError(f"hidden width {H}: the tensor-core path needs a multiple of 32 (>= 32); "
+                                      "width 10 runs on the fused toy kernel")
+        self.H, self.device, self.module = H, dev, module
+        self.engine = engine_for(dev.index if dev.index is not None else torch.cuda.current_device())
+        self.lib = self.engine.lib
+        self.num_tensors = len(tensors)
+        self.P = P = sum(p.numel() for p in tensors)
+        assert P == 3 * H * H + 7 * H + 1
+        with torch.cuda.device(dev):
+            self.params = torch.empty(P, dtype=torch.float32, device=dev)
+            self.grads = torch.zeros(P + 1, dtype=torch.float32, device=dev)
+            self.off = []
+            off = 0
+            for p in tensors:
+                n = p.numel()
+                self.params[off:off + n].copy_(p.data.reshape(-1))
+                p.data = self.params[off:off + n].view(p.shape)
+                p.grad = self.grads[off:off + n].view(p.shape)
+                owners[id(p)] = self
+                self.off.append(off)
+                off += n
+            self.state = torch.zeros(4, dtype=torch.int64, device=dev)
+            ld = self.ld = CAP_B
+            self.act = [torch.empty(CAP_B, H, device=dev) for _ in range(4)]
+            self.act_t = [torch.zeros(H + 1, ld, device=dev) for _ in range(4)]
+            for t in self.act_t:
+                t[H].fill_(1.0)                               # the operand row that turns wgrad's last column into db
+            self.dz = [torch.empty(CAP_B, H, device=dev) for _ in range(2)]
+            self.dz_t = [torch.zeros(H, ld, device=dev) for _ in range(2)]
+            self.out = torch.empty(CAP_B, device=dev)
+            self.dz4 = torch.empty(CAP_B, device=dev)
+            self.sq = torch.empty(CAP_B, device=dev)
+        self.loss_dev = torch.zeros(LOSS_RING, dtype=torch.float32, device=dev)
+        self.loss_host = torch.zeros(LOSS_RING, dtype=torch.float32, pin_memory=True)
+        self.loss_bits = self.loss_host.numpy().view(np.uint32)
+        self._loss_out = ctypes.c_float()
+        self.process_group = process_group
+        self.world, self.rank, self.backend_name = 1, 0, None
+        if dist.is_available() and dist.is_initialized():
+            self.world, self.rank = dist.get_world_size(process_group), dist.get_rank(process_group)
+            self.backend_name = dist.get_backend(process_group)
+        self._sync_replicas()
+        cap = float(os.environ.get("DDPB_BUCKET_CAP_MB", bucket_cap_mb if bucket_cap_mb else 25))
+        self.buckets = self._plan_buckets(cap)
+        self.comm_stream = torch.cuda.Stream(device=dev) if self.world > 1 else None
+        self.opt_kind = self.hyper = self.m = self.v = self.bias_table = None
+        self.seq = 0
+        self.waiting = None
+        self.grads_fresh = False
+        self.fused_exchange = False
+
+    # -- layout ---------------------------------------------------------------------------
+    def _w(self, l):          # data_ptr of W_l / b_l in params, of their gradients in grads
+        return self.params.data_ptr() + 4 * self.off[2 * l], self.params.data_ptr() + 4 * self.off[2 * l + 1]
+
+    def _g(self, l):
+        return self.grads.data_ptr() + 4 * self.off[2 * l], self.grads.data_ptr() + 4 * self.off[2 * l + 1]
+
+    def _plan_buckets(self, cap_mb):
+        """[(layer, start, count)] in reverse parameter order, each layer's range cut at cap_mb."""
+        cap = max(4, int(cap_mb * (1 << 20) / 4) // 4 * 4)
+        out = []
+        for l in range(4, -1, -1):
+            start = self.off[2 * l]
+            end = self.off[2 * l + 2] if l < 4 else self.P
+            while start < end:
+                n = min(cap, end - start)
+                out.append((l, start, n))
+                start += n
+        return out
+
+    def _sync_replicas(self):
+        if self.world == 1:
+            return
+        if self.backend_name == "nccl":
+            comm = self.engine.ensure_comm(self.process_group)
+            _lib.check(self.lib.ddpb_broadcast_f32(comm, self.params.data_ptr(), self.P, 0, self.engine.stream()),
+                       "ddpb_broadcast_f32")
+        else:
+            host = self.params.cpu()
+            dist.broadcast(host, src=0, group=self.process_group)
+            self.params.copy_(host)
+
+    # -- optimizer ------------------------------------------------------------------------
+    def attach_optimizer(self, kind, hyper):
+        self.opt_kind, self.hyper = kind, hyper
+        with torch.cuda.device(self.device):
+            self.m = torch.zeros(self.P, dtype=torch.float32, device=self.device)
+            self.v = torch.zeros(self.P, dtype=torch.float32, device=self.device) if kind == _lib.OPT_ADAM else self.m
+            if kind == _lib.OPT_ADAM:
+                table = _lib.adam_bias_table(hyper["lr"], *hyper["betas"])
+                self.bias_table = torch.from_numpy(table).to(self.device)
+        self.sgd_steps = 0
+
+    def optimizer_state_dict(self):
+        return {"step": int(self.state[0].item()), "exp_avg": self.m, "exp_avg_sq": self.v}
+
+    def discard_pending_backward(self):
+        self.waiting = None
+        self.grads_fresh = False
+
+    def _update(self, start, n, stream, advance):
+        """Fused average + optimizer over grads[start:start+n]."""
+        h, scale = self.hyper, 1.0 / self.world
+        g, p, m = self.grads.data_ptr() + 4 * start, self.params.data_ptr() + 4 * start, self.m.data_ptr() + 4 * start
+        if self.opt_kind == _lib.OPT_ADAM:
+            _lib.check(self.lib.ddpb_fused_avg_adam_dev(g, p, m, self.v.data_ptr() + 4 * start, n, scale, h["betas"][0],
+                                                        h["betas"][1], h["eps"], self.bias_table.data_ptr(),
+                                                        self.bias_table.shape[0], self.state.data_ptr(), int(advance),
+                                                        stream), "ddpb_fused_avg_adam_dev")
+            self.engine.launches += 1 + int(advance)
+        else:
+            _lib.check(self.lib.ddpb_fused_avg_sgd(g, p, m, n, scale, h["lr"], h["momentum"], self.sgd_steps, stream),
+                       "ddpb_fused_avg_sgd")
+            self.engine.launches += 1
+
+    # -- the step ---------------------------------------------------------------------------
+    def _bind(self, data, target):
+        if type(data) is HostBatch:
+            data = data.cuda(self.device)
+        if type(target) is HostBatch:
+            target = target.cuda(self.device)
+        if type(data) is StagedBatch:
+            stage = data.stage
+            stage.copy_now()
+            return stage.dev_x_ptr, stage.dev_y_ptr, None, stage.B, stage
+        if type(data) is DeviceBatch:
+            return data.x.data_ptr(), data.y.data_ptr(), data.idx_ptr, data.B, data.keep
+        if type(target) is StagedBatch:
+            target = target.tensor()
+        if not (isinstance(data, torch.Tensor) and data.is_cuda and data.dtype == torch.float32 and data.dim() == 2
+                and data.shape[1] == 2 and data.is_contiguous()):
+            raise _lib.DdpB200Error("model input must be a contiguous float32 CUDA tensor [B,2] (or a loader batch)")
+        if target is not None and not (isinstance(target, torch.Tensor) and target.is_cuda and target.dtype == torch.float32
+                                       and target.numel() == data.shape[0] and target.is_contiguous()):
+            raise _lib.DdpB200Error("target must be a contiguous float32 CUDA tensor [B,1]")
+        return data.data_ptr(), (target.data_ptr() if target is not None else None), None, data.shape[0], (data, target)
+
+    def _run(self, loss, with_update):
+        x, y, idx, B, keep = self._bind(loss.output.data, loss.target)
+        if B > CAP_B:
+            raise NotImplementedError(f"local batch {B} > {CAP_B} on the widened path")
+        lib, H, ld, eng = self.lib, self.H, self.ld, self.engine
+        stream = eng.stream()
+        slot = loss.slot = self.seq % LOSS_RING
+        self.seq += 1
+        self.loss_bits[slot] = LOSS_SENTINEL
+        loss_slot = self.loss_host.data_ptr() + 4 * slot
+        act, act_t, dz, dz_t = self.act, self.act_t, self.dz, self.dz_t
+        ck = _lib.check
+        # ---- forward
+        w, b = self._w(0)
+        ck(lib.ddpb_wide_first_fwd(x, idx, w, b, act[0].data_ptr(), act_t[0].data_ptr(), B, H, ld, stream), "first_fwd")
+        for l in (1, 2, 3):
+            w, b = self._w(l)
+            ck(lib.ddpb_linear_fwd(act[l - 1].data_ptr(), w, b, act[l].data_ptr(), act_t[l].data_ptr(), B, H, H, ld, 1,
+                                   stream), "linear_fwd")
+        w, b = self._w(4)
+        ck(lib.ddpb_wide_last_fwd(act[3].data_ptr(), w, b, y, idx, self.out.data_ptr(), self.dz4.data_ptr(),
+                                  self.sq.data_ptr(), B, H, stream), "last_fwd")
+        # ---- backward; a layer's bucket(s) go to the communication stream as soon as they are produced
+        gw, gb = self._g(4)
+        ck(lib.ddpb_wide_last_bwd(act[3].data_ptr(), w, self.dz4.data_ptr(), self.sq.data_ptr(), dz[0].data_ptr(),
+                                  dz_t[0].data_ptr(), gw, gb, self.grads.data_ptr() + 4 * self.P, loss_slot, B, H, ld,
+                                  stream), "last_bwd")
+        eng.launches += 6
+        self._layer_done(4, with_update)
+        cur = 0
+        for l in (3, 2, 1):
+            w, _ = self._w(l)
+            gw, gb = self._g(l)
+            ck(lib.ddpb_linear_wgrad(dz_t[cur].data_ptr(), act_t[l - 1].data_ptr(), gw, gb, B, H, H, ld, stream), "wgrad")
+            self._layer_done(l, with_update)
+            ck(lib.ddpb_linear_dgrad(dz[cur].data_ptr(), w, act[l - 1].data_ptr(), dz[1 - cur].data_ptr(),
+                                     dz_t[1 - cur].data_ptr(), B, H, H, ld, stream), "dgrad")
+            cur = 1 - cur
+            eng.launches += 2
+        gw, gb = self._g(0)
+        ck(lib.ddpb_wide_first_bwd(dz[cur].data_ptr(), x, idx, gw, gb, B, H, stream), "first_bwd")
+        eng.launches += 1
+        self._layer_done(0, with_update)
+        self.keep = keep
+        if self.world > 1:
+            torch.cuda.current_stream(self.device).wait_stream(self.comm_stream)    # parameters are final after this
+        elif with_update:
+            self.sgd_steps += 1
+            self._update(0, self.P, stream, True)
+        self.grads_fresh = not with_update
+
+    def _layer_done(self, layer, with_update):
+        """Several ranks: all-reduce (and update) the buckets of `layer` on the communication stream."""
+        if self.world == 1:
+            return
+        if layer == 4:
+            self.sgd_steps += int(with_update)
+        self.comm_stream.wait_stream(torch.cuda.current_stream(self.device))
+        cs = self.comm_stream.cuda_stream
+        mine = [bk for bk in self.buckets if bk[0] == layer]
+        for _, start, n in mine:
+            ptr = self.grads.data_ptr() + 4 * start
+            if self.backend_name == "nccl":
+                _lib.check(self.lib.ddpb_allreduce_sum_f32(self.engine.comm, ptr, n, cs), "ddpb_allreduce_sum_f32")
+            else:
+                with torch.cuda.stream(self.comm_stream):
+                    host = self.grads[start:start + n].cpu()
+                    dist.all_reduce(host, group=self.process_group)
+                    self.grads[start:start + n].copy_(host)
+            if with_update:
+                last = layer == 0 and (start + n) == self.off[2]
+                self._update(start, n, cs, last)
+
+    def request_backward(self, loss):
+        if self.waiting is not None and self.waiting is not loss:
+            self._run(self.waiting, False)
+        if self.opt_kind is not None:
+            self.waiting = loss
+        else:
+            self.waiting = None
+            self._run(loss, False)
+
+    def request_step(self):
+        if self.opt_kind is None:
+            raise _lib.DdpB200Error("no optimizer attached")
+        if self.waiting is not None:
+            loss, self.waiting = self.waiting, None
+            self._run(loss, True)
+            return
+        if not self.grads_fresh:
+            return
+        self.grads_fresh = False
+        self.sgd_steps += 1
+        self._update(0, self.P, self.engine.stream(), True)      # gradients are already averaged? no: scaled inside
+
+    # -- results ------------------------------------------------------------------------------
+    def read_loss(self, loss):
+        if loss.slot is None:
+            if self.waiting is loss:
+                self.waiting = None
+            self._run(loss, False)
+        _lib.check(self.lib.ddpb_wait_f32(self.loss_host.data_ptr() + 4 * loss.slot, LOSS_SENTINEL, 2_000_000,
+                                          self.engine.stream(), ctypes.byref(self._loss_out)), "ddpb_wait_f32")
+        return torch.tensor(self._loss_out.value)
+
+    def loss_device_view(self, loss):
+        return self.read_loss(loss).to(self.device)
+
+    def forward_now(self, data):
+        x, _, idx, B, keep = self._bind(data, None)
+        lib, H, ld, stream = self.lib, self.H, self.ld, self.engine.stream()
+        w, b = self._w(0)
+        _lib.check(lib.ddpb_wide_first_fwd(x, idx, w, b, self.act[0].data_ptr(), self.act_t[0].data_ptr(), B, H, ld, stream))
+        for l in (1, 2, 3):
+            w, b = self._w(l)
+            _lib.check(lib.ddpb_linear_fwd(self.act[l - 1].data_ptr(), w, b, self.act[l].data_ptr(), None, B, H, H, ld, 1, stream))
+        w, b = self._w(4)
+        _lib.check(lib.ddpb_wide_last_fwd(self.act[3].data_ptr(), w, b, None, None, self.out.data_ptr(), None, None, B, H, stream))
+        return self.out[:B].clone().view(B, 1)
+
+    def check_peers(self):
+        pass

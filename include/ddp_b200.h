@@ -198,6 +198,18 @@ int ddpb_linear_dgrad(const float *dz, const float *W, const float *act_prev, fl
 int ddpb_linear_wgrad(const float *dz_t, const float *act_t_ext, float *dW, float *db, int B, int Hin, int Hout,
                       int ld_t, void *stream);
 
+/* The thin ends of the widened model (first Linear 2->H + LeakyReLU, toy_model_and_data.py:13-14;
+ * last Linear H->1, :21; nn.MSELoss and its backward, demo.py:106-109): streaming kernels, B <= 256.
+ * idx (optional) gathers rows of x / y from the HBM-resident dataset. */
+int ddpb_wide_first_fwd(const float *x, const int32_t *idx, const float *W0, const float *b0, float *act, float *act_t,
+                        int B, int H, int ld_t, void *stream);
+int ddpb_wide_last_fwd(const float *act3, const float *W4, const float *b4, const float *y, const int32_t *idx,
+                       float *out, float *dz4, float *sq, int B, int H, void *stream);
+int ddpb_wide_last_bwd(const float *act3, const float *W4, const float *dz4, const float *sq, float *dz3, float *dz3_t,
+                       float *gW4, float *gb4, float *sq_sum_out, float *loss_slot, int B, int H, int ld_t, void *stream);
+int ddpb_wide_first_bwd(const float *dz0, const float *x, const int32_t *idx, float *gW0, float *gb0, int B, int H,
+                        void *stream);
+
 /* ---- optimizer over a flat bucket ----------------------------------------- */
 /* One pass over a (reduced) gradient bucket: g = bucket * grad_scale (the 1/W of
  * DDP's averaging, torch:distributed/algorithms/ddp_comm_hooks/default_hooks.py:24-29),

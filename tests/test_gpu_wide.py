@@ -84,3 +84,62 @@ def test_linear_wgrad(native_lib, B, Hin, Hout):
                                             ld, _stream()))
     _close(dW, dz_t[:, :B] @ act_t[:Hin, :B].t())
     _close(db, dz_t[:, :B].sum(dim=1))
+
+
+def _torch_twin(model):
+    """Stock fp32 torch modules carrying the wrapped model's current parameters."""
+    H = model.module.hidden
+    dims = (2, H, H, H, H, 1)
+    layers = []
+    for i in range(5):
+        layers.append(torch.nn.Linear(dims[i], dims[i + 1]))
+        if i < 4:
+            layers.append(torch.nn.LeakyReLU())
+    twin = torch.nn.Sequential(*layers).cuda()
+    flat = model.flat_parameters()
+    off = 0
+    with torch.no_grad():
+        for p in twin.parameters():
+            p.copy_(flat[off:off + p.numel()].view_as(p))
+            off += p.numel()
+    return twin
+
+
+@pytest.mark.parametrize("H,B", [(128, 256), (256, 100), (512, 64)])
+def test_widened_model_gradients_and_training(H, B):
+    import distributed_training_pytorch_b200 as b200
+    torch.manual_seed(H)
+    model = b200.DistributedDataParallel(b200.ToyModel(hidden=H).cuda(), device_ids=[0])
+    twin = _torch_twin(model)
+    opt = b200.optim.Adam(model.parameters(), lr=1e-3)
+    opt_t = torch.optim.Adam(twin.parameters(), lr=1e-3)
+    loss_fn = b200.nn.MSELoss()
+    g = torch.Generator(device="cuda").manual_seed(1)
+    z = torch.randn(512, device="cuda", generator=g)
+    X = torch.stack([z, z], 1).contiguous()
+    Y = (0.5 * torch.randn(512, device="cuda", generator=g) + z * z).view(512, 1).contiguous()
+    # one gradient evaluation, read before the optimizer runs
+    x, y = X[:B].contiguous(), Y[:B].contiguous()
+    loss = loss_fn(model(x), y)
+    loss.backward()
+    lv = float(loss.detach().cpu())
+    lt = torch.nn.functional.mse_loss(twin(x), y)
+    lt.backward()
+    assert abs(lv - lt.item()) <= 4e-3 * abs(lt.item())
+    for (name, p), q in zip(model.module.named_parameters(), twin.parameters()):
+        scale = q.grad.abs().max().item()
+        assert (p.grad - q.grad).abs().max().item() <= 1e-2 * scale + 1e-7, name
+    opt.step()
+    opt_t.step()
+    # a short training run: losses track the fp32 run within the tf32 tolerance
+    for it in range(15):
+        sel = torch.randperm(512, device="cuda", generator=g)[:B]
+        x, y = X[sel].contiguous(), Y[sel].contiguous()
+        opt.zero_grad(set_to_none=True); opt_t.zero_grad(set_to_none=True)
+        loss = loss_fn(model(x), y); loss.backward(); opt.step()
+        lt = torch.nn.functional.mse_loss(twin(x), y); lt.backward(); opt_t.step()
+        assert abs(float(loss.detach().cpu()) - lt.item()) <= 2e-2 * abs(lt.item()), it
+    flat_t = torch.cat([p.detach().reshape(-1) for p in twin.parameters()])
+    assert (model.flat_parameters() - flat_t).abs().max().item() <= 5e-3
+    out = model(x).tensor()
+    assert (out - twin(x)).abs().max().item() <= 4e-3 * twin(x).abs().max().item()
