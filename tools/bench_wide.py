@@ -1,0 +1,80 @@
+#!/usr/bin/env python3
+"""Widened-model measurements (BASELINE.json configs[4]): step time and per-kernel roofline
+fractions of the tcgen05 GEMMs and the fused Adam pass, CUDA events, one GPU.
+
+    python tools/bench_wide.py [--hidden 1024 4096 8192] [--batch 256] [--steps 20]
+Prints one JSON line per width."""
+import argparse
+import json
+import os
+import sys
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import distributed_training_pytorch_b200 as b200  # noqa: E402
+from distributed_training_pytorch_b200 import _lib  # noqa: E402
+
+
+def timed(fn, reps, flush):
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(reps)]
+    for a, b in ev:
+        if flush is not None:
+            flush.fill_(1)
+        a.record(); fn(); b.record()
+    torch.cuda.synchronize()
+    t = sorted(a.elapsed_time(b) for a, b in ev)
+    return t[len(t) // 2]
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--hidden", type=int, nargs="+", default=[1024, 4096, 8192])
+    ap.add_argument("--batch", type=int, default=256)
+    ap.add_argument("--steps", type=int, default=20)
+    a = ap.parse_args()
+    peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0}
+    L = _lib.lib()
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    for H in a.hidden:
+        B = a.batch
+        torch.manual_seed(0)
+        model = b200.DistributedDataParallel(b200.ToyModel(hidden=H).cuda(), device_ids=[0])
+        opt = b200.optim.Adam(model.parameters(), lr=1e-3)
+        loss_fn = b200.nn.MSELoss()
+        z = torch.randn(B, device="cuda")
+        x = torch.stack([z, z], 1).contiguous(); y = (z * z).view(B, 1).contiguous()
+
+        def step():
+            l = loss_fn(model(x), y); l.backward(); opt.step()
+        for _ in range(3):
+            step()
+        torch.cuda.synchronize()
+        ms_step = timed(step, a.steps, None)
+        be = model._backend
+        st = torch.cuda.current_stream().cuda_stream
+        w, bias = be._w(2)
+        gw, gb = be._g(2)
+        P = be.P
+        k = {}
+        k["fwd"] = timed(lambda: L.ddpb_linear_fwd(be.act[0].data_ptr(), w, bias, be.act[1].data_ptr(), be.act_t[1].data_ptr(), B, H, H, be.ld, 1, st), a.steps, flush)
+        k["dgrad"] = timed(lambda: L.ddpb_linear_dgrad(be.dz[0].data_ptr(), w, be.act[0].data_ptr(), be.dz[1].data_ptr(), be.dz_t[1].data_ptr(), B, H, H, be.ld, st), a.steps, flush)
+        k["wgrad"] = timed(lambda: L.ddpb_linear_wgrad(be.dz_t[0].data_ptr(), be.act_t[0].data_ptr(), gw, gb, B, H, H, be.ld, st), a.steps, flush)
+        k["adam"] = timed(lambda: be._update(0, P, st, False), a.steps, flush)
+        wbytes = 4.0 * H * H
+        flops = 2.0 * B * H * H
+        line = {"hidden": H, "batch": B, "params": P, "ms_per_step": ms_step, "samples_per_s": B / (ms_step * 1e-3),
+                "kernels_ms": k,
+                "gemm_hbm_frac": {n: wbytes / (k[n] * 1e-3) / 1e9 / peaks["hbm_gbs"] for n in ("fwd", "dgrad", "wgrad")},
+                "gemm_tflops": {n: flops / (k[n] * 1e-3) / 1e12 for n in ("fwd", "dgrad", "wgrad")},
+                "adam_gbs": 28.0 * P / (k["adam"] * 1e-3) / 1e9, "adam_hbm_frac": 28.0 * P / (k["adam"] * 1e-3) / 1e9 / peaks["hbm_gbs"],
+                "step_floor_ms": (40.0 * P / (peaks["hbm_gbs"] * 1e9)) * 1e3,
+                "note": "kernel times: median of CUDA-event pairs with a 256 MiB L2 flush before each; algorithmic bytes 4*H*H per GEMM, 28*P for Adam; step floor = 40 B/param"}
+        print(json.dumps(line), flush=True)
+        del model, opt, be
+        torch.cuda.empty_cache()
+
+
+if __name__ == "__main__":
+    main()
