@@ -5,7 +5,7 @@
 // Reference: the same nn.Linear layers (toy_model_and_data.py:13-21, widths scaled up) that
 // PyTorch runs as cuBLAS sgemm calls in forward and in autograd's backward (demo.py:104-109).
 //
-//   D[m][n] = sum_k A(m,k) * B(n,k)          one 128 x 128 output tile per CTA
+//   D[m][n] = sum_k A(m,k) * B(n,k)          one 128 x BN output tile per CTA (BN = 128 or 64)
 //
 //   forward   m = sample, n = output neuron, k = input neuron   A = act_in [B,Hin]   K-major
 //                                                                B = W [Hout,Hin]      K-major
@@ -31,14 +31,20 @@
 
 namespace {
 
-constexpr int BM = 128, BN = 128, BK = 32;           // BK tf32 = 128 bytes = one swizzle atom row
-constexpr int kStages = 6;
+constexpr int BM = 128, BK = 32;                     // BK tf32 = 128 bytes = one swizzle atom row
 constexpr int kThreads = 256;
-constexpr int kTileBytes = BM * BK * 4;              // 16 KB per operand tile
-constexpr int kStageBytes = 2 * kTileBytes;
-constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*alignment slack*/ + 256 /*barriers*/;
-constexpr int kTmemCols = BN;                        // fp32 accumulator: 128 lanes x 128 columns
+constexpr int kATileBytes = BM * BK * 4;             // 16 KB
 constexpr float kSlope = 0.01f;
+
+// Tile configuration by output-tile width BN (128, or 64 when 128-wide tiles would leave most of
+// the 148 SMs without a CTA): bytes per pipeline stage, ring depth, dynamic shared memory.
+template <int BN> struct Cfg {
+    static constexpr int kBTileBytes = BN * BK * 4;
+    static constexpr int kStageBytes = kATileBytes + kBTileBytes;
+    static constexpr int kStages = BN == 128 ? 6 : 8;
+    static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*alignment slack*/ + 256 /*barriers*/;
+    static constexpr int kTmemCols = BN;             // fp32 accumulator: 128 lanes x BN columns
+};
 
 enum { EPI_FWD = 0, EPI_DGRAD = 1, EPI_WGRAD = 2 };
 
@@ -129,6 +135,7 @@ __device__ __forceinline__ unsigned long long make_desc(unsigned smem_byte_addr,
 }
 
 // Instruction descriptor: fp32 accumulate, tf32 x tf32, M = 128, N = BN.
+template <int BN>
 __device__ __forceinline__ unsigned make_idesc(bool b_mn_major) {
     unsigned d = 0;
     d |= 1u << 4;                          // D format F32
@@ -140,10 +147,11 @@ __device__ __forceinline__ unsigned make_idesc(bool b_mn_major) {
     return d;
 }
 
-template <int EPI, bool B_MN>
+template <int EPI, bool B_MN, int BN>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                  const EpiParams ep, int M, int N, int K) {
+    constexpr int kStages = Cfg<BN>::kStages, kStageBytes = Cfg<BN>::kStageBytes, kTmemCols = Cfg<BN>::kTmemCols;
     extern __shared__ unsigned char smem_raw[];
     // 1024-byte alignment for the swizzle atoms
     unsigned char *smem = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -178,7 +186,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
                 const int s = kb % kStages;
                 if (kb >= kStages) mbar_wait(saddr(&bars[kStages + s]), ((kb / kStages) - 1) & 1);
                 const unsigned full = saddr(&bars[s]);
-                const unsigned a_dst = saddr(smem + s * kStageBytes), b_dst = a_dst + kTileBytes;
+                const unsigned a_dst = saddr(smem + s * kStageBytes), b_dst = a_dst + kATileBytes;
                 mbar_expect_tx(full, kStageBytes);
                 tma_load_2d(a_dst, &map_a, full, kb * BK, m0);                       // [128 rows][32 k]
                 if (!B_MN) {
@@ -193,12 +201,12 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     } else if (warp == 1) {
         // ===== MMA issuer (one thread) =====
         if (lane == 0) {
-            const unsigned idesc = make_idesc(B_MN);
+            const unsigned idesc = make_idesc<BN>(B_MN);
             for (int kb = 0; kb < num_k; ++kb) {
                 const int s = kb % kStages;
                 mbar_wait(saddr(&bars[s]), (kb / kStages) & 1);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                const unsigned a_base = saddr(smem + s * kStageBytes), b_base = a_base + kTileBytes;
+                const unsigned a_base = saddr(smem + s * kStageBytes), b_base = a_base + kATileBytes;
 #pragma unroll
                 for (int k = 0; k < BK / 8; ++k) {                                   // UMMA_K = 8 for tf32
                     const unsigned long long da = make_desc(a_base + k * 32, 0, 1024, 2);
@@ -308,18 +316,23 @@ int make_map(CUtensorMap *map, const float *base, long long rows, long long cols
     return 0;
 }
 
-template <int EPI, bool B_MN>
+template <int EPI, bool B_MN, int BN>
 int launch(const CUtensorMap &ma, const CUtensorMap &mb, const EpiParams &ep, int M, int N, int K, cudaStream_t stream) {
     static bool configured = false;
     if (!configured) {
-        DDPB_CUDA(cudaFuncSetAttribute(gemm_tf32_kernel<EPI, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+        DDPB_CUDA(cudaFuncSetAttribute(gemm_tf32_kernel<EPI, B_MN, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       Cfg<BN>::kSmemBytes));
         configured = true;
     }
     dim3 grid((N + BN - 1) / BN, (M + BM - 1) / BM, 1);
-    gemm_tf32_kernel<EPI, B_MN><<<grid, kThreads, kSmemBytes, stream>>>(ma, mb, ep, M, N, K);
+    gemm_tf32_kernel<EPI, B_MN, BN><<<grid, kThreads, Cfg<BN>::kSmemBytes, stream>>>(ma, mb, ep, M, N, K);
     DDPB_CUDA(cudaGetLastError());
     return 0;
 }
+
+// 64-wide tiles when 128-wide ones would occupy fewer than ~3/4 of the SMs (weights are streamed
+// once either way; more CTAs = more TMA streams in flight).
+bool narrow_tiles(int M, int N) { return (long long)((M + BM - 1) / BM) * ((N + 127) / 128) < 112; }
 
 }  // namespace
 
@@ -330,9 +343,11 @@ DDPB_API int ddpb_linear_fwd(const float *act_in, const float *W, const float *b
     DDPB_REQUIRE(!act_out_t || ld_t >= B, "ddpb_linear_fwd: transposed pitch %d < batch %d", ld_t, B);
     CUtensorMap ma, mb;
     if (int rc = make_map(&ma, act_in, B, Hin, Hin, BM, BK)) return rc;
-    if (int rc = make_map(&mb, W, Hout, Hin, Hin, BN, BK)) return rc;
+    const bool narrow = narrow_tiles(B, Hout);
+    if (int rc = make_map(&mb, W, Hout, Hin, Hin, narrow ? 64 : 128, BK)) return rc;
     EpiParams ep = {bias, nullptr, act_out, act_out_t, Hout, ld_t, apply_act, 0};
-    return launch<EPI_FWD, false>(ma, mb, ep, B, Hout, Hin, (cudaStream_t)stream);
+    return narrow ? launch<EPI_FWD, false, 64>(ma, mb, ep, B, Hout, Hin, (cudaStream_t)stream)
+                  : launch<EPI_FWD, false, 128>(ma, mb, ep, B, Hout, Hin, (cudaStream_t)stream);
 }
 
 DDPB_API int ddpb_linear_dgrad(const float *dz, const float *W, const float *act_prev, float *dz_prev, float *dz_prev_t,
@@ -344,7 +359,8 @@ DDPB_API int ddpb_linear_dgrad(const float *dz, const float *W, const float *act
     if (int rc = make_map(&ma, dz, B, Hout, Hout, BM, BK)) return rc;                 // A: [m = sample][k = out neuron]
     if (int rc = make_map(&mb, W, Hout, Hin, Hin, BK, 32, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B)) return rc;   // B: boxes [32 k][32 n], n contiguous
     EpiParams ep = {nullptr, act_prev, dz_prev, dz_prev_t, Hin, ld_t, 0, 0};
-    return launch<EPI_DGRAD, true>(ma, mb, ep, B, Hin, Hout, (cudaStream_t)stream);
+    return narrow_tiles(B, Hin) ? launch<EPI_DGRAD, true, 64>(ma, mb, ep, B, Hin, Hout, (cudaStream_t)stream)
+                                : launch<EPI_DGRAD, true, 128>(ma, mb, ep, B, Hin, Hout, (cudaStream_t)stream);
 }
 
 DDPB_API int ddpb_linear_wgrad(const float *dz_t, const float *act_t_ext, float *dW, float *db, int B, int Hin, int Hout,
@@ -353,7 +369,7 @@ DDPB_API int ddpb_linear_wgrad(const float *dz_t, const float *act_t_ext, float 
                  "ddpb_linear_wgrad: bad arguments (B=%d Hin=%d Hout=%d ld_t=%d)", B, Hin, Hout, ld_t);
     CUtensorMap ma, mb;
     if (int rc = make_map(&ma, dz_t, Hout, B, ld_t, BM, BK)) return rc;               // A: [m = out neuron][k = sample]
-    if (int rc = make_map(&mb, act_t_ext, Hin + 1, B, ld_t, BN, BK)) return rc;       // B: [n = in neuron | ones][k = sample]
+    if (int rc = make_map(&mb, act_t_ext, Hin + 1, B, ld_t, 128, BK)) return rc;      // B: [n = in neuron | ones][k = sample]
     EpiParams ep = {nullptr, nullptr, dW, db, Hin, 0, 0, Hin};
-    return launch<EPI_WGRAD, false>(ma, mb, ep, Hout, Hin + 1, B, (cudaStream_t)stream);
+    return launch<EPI_WGRAD, false, 128>(ma, mb, ep, Hout, Hin + 1, B, (cudaStream_t)stream);
 }

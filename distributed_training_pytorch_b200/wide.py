@@ -61,8 +61,11 @@ class WideBackend:
             self.act_t = [torch.zeros(H + 1, ld, device=dev) for _ in range(4)]
             for t in self.act_t:
                 t[H].fill_(1.0)                               # the operand row that turns wgrad's last column into db
-            self.dz = [torch.empty(CAP_B, H, device=dev) for _ in range(2)]
-            self.dz_t = [torch.zeros(H, ld, device=dev) for _ in range(2)]
+            # one pre-activation-gradient buffer (+ transpose) per layer 3..0: wgrad of a layer runs on a
+            # side stream while dgrad produces the next layer's buffer, so nothing is reused in flight
+            self.dz = [torch.empty(CAP_B, H, device=dev) for _ in range(4)]
+            self.dz_t = [torch.zeros(H, ld, device=dev) for _ in range(4)]
+            self.side_stream = torch.cuda.Stream(device=dev)
             self.out = torch.empty(CAP_B, device=dev)
             self.dz4 = torch.empty(CAP_B, device=dev)
             self.sq = torch.empty(CAP_B, device=dev)
@@ -200,21 +203,24 @@ class WideBackend:
                                   dz_t[0].data_ptr(), gw, gb, self.grads.data_ptr() + 4 * self.P, loss_slot, B, H, ld,
                                   stream), "last_bwd")
         eng.launches += 6
-        self._layer_done(4, with_update)
+        self._layer_done(4, with_update, None)
+        main, side = torch.cuda.current_stream(self.device), self.side_stream
         cur = 0
         for l in (3, 2, 1):
             w, _ = self._w(l)
             gw, gb = self._g(l)
-            ck(lib.ddpb_linear_wgrad(dz_t[cur].data_ptr(), act_t[l - 1].data_ptr(), gw, gb, B, H, H, ld, stream), "wgrad")
-            self._layer_done(l, with_update)
-            ck(lib.ddpb_linear_dgrad(dz[cur].data_ptr(), w, act[l - 1].data_ptr(), dz[1 - cur].data_ptr(),
-                                     dz_t[1 - cur].data_ptr(), B, H, H, ld, stream), "dgrad")
-            cur = 1 - cur
+            side.wait_stream(main)                                # dz_t[cur] is complete on the main stream
+            ck(lib.ddpb_linear_wgrad(dz_t[cur].data_ptr(), act_t[l - 1].data_ptr(), gw, gb, B, H, H, ld, side.cuda_stream), "wgrad")
+            self._layer_done(l, with_update, side)
+            ck(lib.ddpb_linear_dgrad(dz[cur].data_ptr(), w, act[l - 1].data_ptr(), dz[cur + 1].data_ptr(),
+                                     dz_t[cur + 1].data_ptr(), B, H, H, ld, stream), "dgrad")
+            cur += 1
             eng.launches += 2
         gw, gb = self._g(0)
         ck(lib.ddpb_wide_first_bwd(dz[cur].data_ptr(), x, idx, gw, gb, B, H, stream), "first_bwd")
         eng.launches += 1
-        self._layer_done(0, with_update)
+        self._layer_done(0, with_update, None)
+        main.wait_stream(side)
         self.keep = keep
         if self.world > 1:
             torch.cuda.current_stream(self.device).wait_stream(self.comm_stream)    # parameters are final after this
@@ -223,13 +229,14 @@ class WideBackend:
             self._update(0, self.P, stream, True)
         self.grads_fresh = not with_update
 
-    def _layer_done(self, layer, with_update):
-        """Several ranks: all-reduce (and update) the buckets of `layer` on the communication stream."""
+    def _layer_done(self, layer, with_update, produced_on):
+        """Several ranks: all-reduce (and update) the buckets of `layer` on the communication stream,
+        after the stream that produced them (`produced_on`, default the main stream)."""
         if self.world == 1:
             return
         if layer == 4:
             self.sgd_steps += int(with_update)
-        self.comm_stream.wait_stream(torch.cuda.current_stream(self.device))
+        self.comm_stream.wait_stream(produced_on if produced_on is not None else torch.cuda.current_stream(self.device))
         cs = self.comm_stream.cuda_stream
         mine = [bk for bk in self.buckets if bk[0] == layer]
         for _, start, n in mine:
