@@ -153,3 +153,10 @@ def test_adam_bias_table_is_torchs_python_arithmetic():
         bc1, bc2 = 1 - 0.9 ** t, 1 - 0.999 ** t                   # torch:optim/adam.py:531-536
         assert table[t - 1, 0] == np.float32(-(1e-3 / bc1)) and table[t - 1, 1] == np.float32(bc2 ** 0.5)
     assert table[-1].tolist() == [np.float32(-1e-3), 1.0]        # converged: later steps reuse the last row
+
+
+def test_cached_epoch_blocks_equal_single_epoch_calls():
+    s = b200.DistributedSampler(_Range(512), num_replicas=4, rank=3, shuffle=True)
+    for epoch in (0, 1, 63, 64, 65, 200, 5):
+        s.set_epoch(epoch)
+        assert np.array_equal(s.cached_indices(), s.indices())
