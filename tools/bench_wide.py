@@ -28,12 +28,63 @@ def timed(fn, reps, flush):
     return t[len(t) // 2]
 
 
+def sweep(a, world):
+    """Several ranks (torchrun): step time of the widened model per bucket cap; the NVLink side of the
+    roofline is the all-reduce of 4*P bytes (bus factor 2(W-1)/W) against 770 GB/s measured per direction."""
+    import torch.distributed as dist
+    rank, local = int(os.environ["RANK"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    side = dist.new_group(backend="gloo")
+    caps = a.bucket_caps or [1, 5, 25, 100, 400, 1e9]
+    for H in a.hidden:
+        B = max(1, min(a.batch, 512 // world))
+        for cap in caps:
+            torch.manual_seed(0)
+            model = b200.DistributedDataParallel(b200.ToyModel(hidden=H).cuda(), device_ids=[local], bucket_cap_mb=cap)
+            opt = b200.optim.Adam(model.parameters(), lr=1e-3)
+            loss_fn = b200.nn.MSELoss()
+            g = torch.Generator(device="cuda").manual_seed(rank)
+            z = torch.randn(B, device="cuda", generator=g)
+            x = torch.stack([z, z], 1).contiguous(); y = (z * z).view(B, 1).contiguous()
+
+            def step():
+                l = loss_fn(model(x), y); l.backward(); opt.step()
+            for _ in range(3):
+                step()
+            dist.barrier(); torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(a.steps):
+                step()
+            e1.record(); torch.cuda.synchronize()
+            t = torch.tensor([e0.elapsed_time(e1) / a.steps], dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX, group=side)
+            P = model._backend.P
+            if rank == 0:
+                ms = float(t)
+                wire = 2.0 * (world - 1) / world * 4.0 * P
+                print(json.dumps({"hidden": H, "world": world, "local_batch": B, "bucket_cap_mb": cap,
+                                  "buckets": len(model._backend.buckets), "ms_per_step": ms,
+                                  "samples_per_s": B * world / (ms * 1e-3),
+                                  "allreduce_wire_bytes_per_gpu": wire,
+                                  "nvlink_floor_ms": wire / 770e9 * 1e3, "hbm_floor_ms": 40.0 * P / 6545.3e9 * 1e3}), flush=True)
+            del model, opt
+            torch.cuda.empty_cache()
+    dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--hidden", type=int, nargs="+", default=[1024, 4096, 8192])
     ap.add_argument("--batch", type=int, default=256)
     ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--bucket-caps", type=float, nargs="+", default=None,
+                    help="under torchrun: sweep bucket_cap_mb (step time per cap, max over ranks)")
     a = ap.parse_args()
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if world > 1:
+        return sweep(a, world)
     peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0}
     L = _lib.lib()
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
