@@ -18,6 +18,10 @@
 //             epilogue: store dW straight into the flat gradient bucket; the operand row
 //             n = Hin is a row of ones, which makes column Hin of the product the bias gradient
 //
+// CTAs that compute neighbouring n-tiles of the same m-tile form a cluster of 4 (2, 1): each loads a
+// quarter of the shared A slab and TMA-multicasts it to all four, and a stage is released by
+// tcgen05.commit multicast to every CTA that filled part of it -- the A slab crosses L2 once
+// per cluster instead of once per tile (the kernels were L2-bound without it, profiles/).
 // Structure (one CTA, 256 threads): warp 0 = TMA producer, warp 1 = MMA issuer (one elected
 // thread), warp 2 = TMEM allocator, warps 4..7 = epilogue (tcgen05.ld 32 lanes x 32 columns at a
 // time).  A 6-stage ring of {A tile, B tile} (32 KB per stage, 128-byte swizzle) is filled by
@@ -28,6 +32,7 @@
 // feeds 128 FLOP per pass): the roofline is weight bytes / HBM bandwidth.
 #include "common.cuh"
 #include <cuda.h>
+#include <cstdlib>
 
 namespace {
 
@@ -81,6 +86,28 @@ __device__ __forceinline__ void tma_load_2d(unsigned dst, const CUtensorMap *map
     asm volatile(
         "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
         ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1) : "memory");
+}
+// The same load delivered to the same shared-memory offset of every CTA in `mask` (and counted
+// on each of their mbarriers): CTAs of a cluster that need the same A slab fetch it from L2 once.
+__device__ __forceinline__ void tma_load_2d_multicast(unsigned dst, const CUtensorMap *map, unsigned bar, int c0, int c1,
+                                                      unsigned short mask) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster "
+        "[%0], [%1, {%3, %4}], [%2], %5;"
+        ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "h"(mask) : "memory");
+}
+__device__ __forceinline__ void umma_commit_multicast(unsigned bar, unsigned short mask) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(bar), "h"(mask) : "memory");
+}
+__device__ __forceinline__ unsigned cluster_ctarank() {
+    unsigned r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
 __device__ __forceinline__ void tmem_alloc(unsigned slot_smem, unsigned cols) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(slot_smem), "r"(cols) : "memory");
@@ -147,7 +174,7 @@ __device__ __forceinline__ unsigned make_idesc(bool b_mn_major) {
     return d;
 }
 
-template <int EPI, bool B_MN, int BN>
+template <int EPI, bool B_MN, int BN, int CL>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                  const EpiParams ep, int M, int N, int K) {
@@ -163,10 +190,14 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     const int n0 = blockIdx.x * BN, m0 = blockIdx.y * BM;
     const int num_k = (K + BK - 1) / BK;
 
+    // CL > 1: the CL CTAs of a cluster compute CL neighbouring n-tiles of the same m-tile; each loads
+    // 1/CL of the shared A slab and multicasts it, so a stage is free only when all CL have used it.
+    const unsigned crank = CL > 1 ? cluster_ctarank() : 0u;
+    constexpr unsigned short kMask = (unsigned short)((1u << CL) - 1u);
     if (threadIdx.x == 0) {
         for (int s = 0; s < kStages; ++s) {
             mbar_init(saddr(&bars[s]), 1);
-            mbar_init(saddr(&bars[kStages + s]), 1);
+            mbar_init(saddr(&bars[kStages + s]), CL);
         }
         mbar_init(saddr(&bars[2 * kStages]), 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -176,6 +207,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     if (warp == 2) tmem_alloc(saddr(tmem_slot), kTmemCols);
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
+    if (CL > 1) cluster_sync_all();                    // peers' barriers exist before anything is multicast
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const unsigned tmem_base = *tmem_slot;
 
@@ -188,7 +220,13 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
                 const unsigned full = saddr(&bars[s]);
                 const unsigned a_dst = saddr(smem + s * kStageBytes), b_dst = a_dst + kATileBytes;
                 mbar_expect_tx(full, kStageBytes);
-                tma_load_2d(a_dst, &map_a, full, kb * BK, m0);                       // [128 rows][32 k]
+                if (CL == 1) {
+                    tma_load_2d(a_dst, &map_a, full, kb * BK, m0);                   // [128 rows][32 k]
+                } else {
+                    constexpr int kSliceRows = BM / CL;                              // my share of the slab, for everyone
+                    tma_load_2d_multicast(a_dst + crank * kSliceRows * BK * 4, &map_a, full, kb * BK,
+                                          m0 + (int)crank * kSliceRows, kMask);
+                }
                 if (!B_MN) {
                     tma_load_2d(b_dst, &map_b, full, kb * BK, n0);                   // [128 rows][32 k]
                 } else {
@@ -214,7 +252,8 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
                                                        : make_desc(b_base + k * 32, 0, 1024, 2);
                     umma_tf32(tmem_base, da, db, idesc, (kb | k) != 0);
                 }
-                umma_commit(saddr(&bars[kStages + s]));                              // frees the stage when the MMAs retire
+                if (CL == 1) umma_commit(saddr(&bars[kStages + s]));                 // frees the stage when the MMAs retire
+                else umma_commit_multicast(saddr(&bars[kStages + s]), kMask);        // ... in every CTA that filled part of it
             }
             umma_commit(saddr(&bars[2 * kStages]));                                  // accumulator complete
         }
@@ -276,6 +315,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     }
     __syncthreads();
+    if (CL > 1) cluster_sync_all();                    // nobody leaves while a peer may still signal its barriers
     if (warp == 2) {
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         tmem_dealloc(tmem_base, kTmemCols);
@@ -316,18 +356,48 @@ int make_map(CUtensorMap *map, const float *base, long long rows, long long cols
     return 0;
 }
 
-template <int EPI, bool B_MN, int BN>
+template <int EPI, bool B_MN, int BN, int CL>
 int launch(const CUtensorMap &ma, const CUtensorMap &mb, const EpiParams &ep, int M, int N, int K, cudaStream_t stream) {
     static bool configured = false;
     if (!configured) {
-        DDPB_CUDA(cudaFuncSetAttribute(gemm_tf32_kernel<EPI, B_MN, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        DDPB_CUDA(cudaFuncSetAttribute(gemm_tf32_kernel<EPI, B_MN, BN, CL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        Cfg<BN>::kSmemBytes));
         configured = true;
     }
-    dim3 grid((N + BN - 1) / BN, (M + BM - 1) / BM, 1);
-    gemm_tf32_kernel<EPI, B_MN, BN><<<grid, kThreads, Cfg<BN>::kSmemBytes, stream>>>(ma, mb, ep, M, N, K);
-    DDPB_CUDA(cudaGetLastError());
+    const int n_tiles = (N + BN - 1) / BN;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((n_tiles + CL - 1) / CL * CL, (M + BM - 1) / BM, 1);   // whole clusters; surplus tiles only feed their peers
+    cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = Cfg<BN>::kSmemBytes;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr;
+    attr.id = cudaLaunchAttributeClusterDimension;
+    attr.val.clusterDim.x = CL; attr.val.clusterDim.y = 1; attr.val.clusterDim.z = 1;
+    cfg.attrs = &attr;
+    cfg.numAttrs = 1;
+    DDPB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tf32_kernel<EPI, B_MN, BN, CL>, ma, mb, ep, M, N, K));
     return 0;
+}
+
+// Cluster width for the multicast of the shared A slab (DDPB_GEMM_CLUSTER = 1, 2 or 4; default 4).
+int cluster_width() {
+    static int w = 0;
+    if (!w) {
+        const char *e = getenv("DDPB_GEMM_CLUSTER");
+        w = e ? atoi(e) : 4;
+        if (w != 1 && w != 2 && w != 4) w = 4;
+    }
+    return w;
+}
+
+template <int EPI, bool B_MN, int BN>
+int launch_cl(const CUtensorMap &ma1, const CUtensorMap &ma2, const CUtensorMap &ma4, const CUtensorMap &mb,
+              const EpiParams &ep, int M, int N, int K, cudaStream_t stream) {
+    switch (cluster_width()) {
+        case 1: return launch<EPI, B_MN, BN, 1>(ma1, mb, ep, M, N, K, stream);
+        case 2: return launch<EPI, B_MN, BN, 2>(ma2, mb, ep, M, N, K, stream);
+        default: return launch<EPI, B_MN, BN, 4>(ma4, mb, ep, M, N, K, stream);
+    }
 }
 
 // 64-wide tiles when 128-wide ones would occupy fewer than ~3/4 of the SMs (weights are streamed
@@ -342,12 +412,12 @@ DDPB_API int ddpb_linear_fwd(const float *act_in, const float *W, const float *b
                  "ddpb_linear_fwd: bad arguments (B=%d Hin=%d Hout=%d)", B, Hin, Hout);
     DDPB_REQUIRE(!act_out_t || ld_t >= B, "ddpb_linear_fwd: transposed pitch %d < batch %d", ld_t, B);
     CUtensorMap ma, mb;
-    if (int rc = make_map(&ma, act_in, B, Hin, Hin, BM, BK)) return rc;
+    if (int rc = make_map(&ma, act_in, B, Hin, Hin, BM / cluster_width(), BK)) return rc;
     const bool narrow = narrow_tiles(B, Hout);
     if (int rc = make_map(&mb, W, Hout, Hin, Hin, narrow ? 64 : 128, BK)) return rc;
     EpiParams ep = {bias, nullptr, act_out, act_out_t, Hout, ld_t, apply_act, 0};
-    return narrow ? launch<EPI_FWD, false, 64>(ma, mb, ep, B, Hout, Hin, (cudaStream_t)stream)
-                  : launch<EPI_FWD, false, 128>(ma, mb, ep, B, Hout, Hin, (cudaStream_t)stream);
+    return narrow ? launch_cl<EPI_FWD, false, 64>(ma, ma, ma, mb, ep, B, Hout, Hin, (cudaStream_t)stream)
+                  : launch_cl<EPI_FWD, false, 128>(ma, ma, ma, mb, ep, B, Hout, Hin, (cudaStream_t)stream);
 }
 
 DDPB_API int ddpb_linear_dgrad(const float *dz, const float *W, const float *act_prev, float *dz_prev, float *dz_prev_t,
@@ -356,11 +426,11 @@ DDPB_API int ddpb_linear_dgrad(const float *dz, const float *W, const float *act
                  "ddpb_linear_dgrad: bad arguments (B=%d Hin=%d Hout=%d)", B, Hin, Hout);
     DDPB_REQUIRE(!dz_prev_t || ld_t >= B, "ddpb_linear_dgrad: transposed pitch %d < batch %d", ld_t, B);
     CUtensorMap ma, mb;
-    if (int rc = make_map(&ma, dz, B, Hout, Hout, BM, BK)) return rc;                 // A: [m = sample][k = out neuron]
+    if (int rc = make_map(&ma, dz, B, Hout, Hout, BM / cluster_width(), BK)) return rc;   // A: [m = sample][k = out neuron]
     if (int rc = make_map(&mb, W, Hout, Hin, Hin, BK, 32, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B)) return rc;   // B: boxes [32 k][32 n], n contiguous
     EpiParams ep = {nullptr, act_prev, dz_prev, dz_prev_t, Hin, ld_t, 0, 0};
-    return narrow_tiles(B, Hin) ? launch<EPI_DGRAD, true, 64>(ma, mb, ep, B, Hin, Hout, (cudaStream_t)stream)
-                                : launch<EPI_DGRAD, true, 128>(ma, mb, ep, B, Hin, Hout, (cudaStream_t)stream);
+    return narrow_tiles(B, Hin) ? launch_cl<EPI_DGRAD, true, 64>(ma, ma, ma, mb, ep, B, Hin, Hout, (cudaStream_t)stream)
+                                : launch_cl<EPI_DGRAD, true, 128>(ma, ma, ma, mb, ep, B, Hin, Hout, (cudaStream_t)stream);
 }
 
 DDPB_API int ddpb_linear_wgrad(const float *dz_t, const float *act_t_ext, float *dW, float *db, int B, int Hin, int Hout,
@@ -368,8 +438,8 @@ DDPB_API int ddpb_linear_wgrad(const float *dz_t, const float *act_t_ext, float 
     DDPB_REQUIRE(dz_t && act_t_ext && dW && db && B >= 1 && Hin >= 32 && Hout >= 32 && Hin % 4 == 0 && ld_t % 4 == 0 && ld_t >= B,
                  "ddpb_linear_wgrad: bad arguments (B=%d Hin=%d Hout=%d ld_t=%d)", B, Hin, Hout, ld_t);
     CUtensorMap ma, mb;
-    if (int rc = make_map(&ma, dz_t, Hout, B, ld_t, BM, BK)) return rc;               // A: [m = out neuron][k = sample]
+    if (int rc = make_map(&ma, dz_t, Hout, B, ld_t, BM / cluster_width(), BK)) return rc;   // A: [m = out neuron][k = sample]
     if (int rc = make_map(&mb, act_t_ext, Hin + 1, B, ld_t, 128, BK)) return rc;      // B: [n = in neuron | ones][k = sample]
     EpiParams ep = {nullptr, nullptr, dW, db, Hin, 0, 0, Hin};
-    return launch<EPI_WGRAD, false, 128>(ma, mb, ep, Hout, Hin + 1, B, (cudaStream_t)stream);
+    return launch_cl<EPI_WGRAD, false, 128>(ma, ma, ma, mb, ep, Hout, Hin + 1, B, (cudaStream_t)stream);
 }

@@ -26,6 +26,24 @@ LOSS_SENTINEL = 0x7FC0DEAD
 CAP_B = 256          # local batch capacity of the work buffers (the reference's batch_size, demo.py:145)
 
 
+def plan_buckets(offsets, total, cap_mb):
+    """Cut the flat gradient into all-reduce buckets: [(layer, start, count)] in REVERSE layer order
+    (gradients become ready last layer first, torch:nn/parallel/distributed.py:1255-1283), each
+    layer's [weight | bias] range cut into pieces of at most cap_mb MiB (counts stay multiples of 4
+    floats so every piece is 16-byte aligned).  `offsets[2l]` is the start of layer l's weight."""
+    cap = max(4, int(cap_mb * (1 << 20) / 4) // 4 * 4)
+    n_layers = len(offsets) // 2
+    out = []
+    for l in range(n_layers - 1, -1, -1):
+        start = offsets[2 * l]
+        end = offsets[2 * l + 2] if l + 1 < n_layers else total
+        while start < end:
+            n = min(cap, end - start)
+            out.append((l, start, n))
+            start += n
+    return out
+
+
 class WideBackend:
     def __init__(self, module, process_group, bucket_cap_mb, owners):
         tensors = list(module.parameters())
@@ -96,17 +114,7 @@ class WideBackend:
         return self.grads.data_ptr() + 4 * self.off[2 * l], self.grads.data_ptr() + 4 * self.off[2 * l + 1]
 
     def _plan_buckets(self, cap_mb):
-        """[(layer, start, count)] in reverse parameter order, each layer's range cut at cap_mb."""
-        cap = max(4, int(cap_mb * (1 << 20) / 4) // 4 * 4)
-        out = []
-        for l in range(4, -1, -1):
-            start = self.off[2 * l]
-            end = self.off[2 * l + 2] if l < 4 else self.P
-            while start < end:
-                n = min(cap, end - start)
-                out.append((l, start, n))
-                start += n
-        return out
+        return plan_buckets(self.off, self.P, cap_mb)
 
     def _sync_replicas(self):
         if self.world == 1:

@@ -160,3 +160,19 @@ def test_cached_epoch_blocks_equal_single_epoch_calls():
     for epoch in (0, 1, 63, 64, 65, 200, 5):
         s.set_epoch(epoch)
         assert np.array_equal(s.cached_indices(), s.indices())
+
+
+def test_bucket_plan_covers_the_flat_gradient_in_reverse_layer_order():
+    from distributed_training_pytorch_b200.wide import plan_buckets
+    H = 1024
+    sizes = [2 * H, H, H * H, H, H * H, H, H * H, H, H, 1]
+    offsets = [int(x) for x in np.cumsum([0] + sizes[:-1])]
+    total = sum(sizes)
+    for cap in (0.5, 1, 5, 25, 1e9):
+        plan = plan_buckets(offsets, total, cap)
+        assert [l for l, _, _ in plan] == sorted((l for l, _, _ in plan), reverse=True)
+        covered = sorted((s, s + n) for _, s, n in plan)
+        assert covered[0][0] == 0 and covered[-1][1] == total
+        assert all(a[1] == b[0] for a, b in zip(covered, covered[1:]))           # no gaps, no overlap
+        assert all(n * 4 <= max(cap * (1 << 20), 16) for _, _, n in plan)
+    assert len(plan_buckets(offsets, total, 1e9)) == 5 and len(plan_buckets(offsets, total, 1)) == 3 * 5 + 2
