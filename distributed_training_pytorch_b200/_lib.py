@@ -16,8 +16,7 @@ OPT_ADAM, OPT_SGD = 0, 1
 MAX_JOBS = 4
 MAX_PEERS = 8
 XCHG_ROW = 376
-XCHG_DATA_FLOATS = 2 * MAX_PEERS * XCHG_ROW
-XCHG_FLAG_WORDS = 2 * MAX_PEERS * 8
+XCHG_WINDOW_BYTES = 2 * MAX_PEERS * XCHG_ROW * 8
 TOY_HIDDEN, TOY_PARAMS = 10, 371
 
 

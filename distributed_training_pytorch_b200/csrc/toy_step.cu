@@ -124,11 +124,16 @@ __device__ __forceinline__ void optimizer_barrier() {
     asm volatile("bar.sync 2, %0;" ::"n"(kThreads - kComputeThreads) : "memory");
 }
 
-// System-scope accesses to peer-mapped windows (other GPUs' HBM over NVLink, or our own).
-__device__ __forceinline__ void st_relaxed_sys(float *p, float v) { asm volatile("st.relaxed.sys.global.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory"); }
-__device__ __forceinline__ float ld_relaxed_sys(const float *p) { float v; asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory"); return v; }
-__device__ __forceinline__ void st_release_sys(unsigned *p, unsigned v) { asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
-__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned *p) { unsigned v; asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory"); return v; }
+// System-scope 8-byte {value, ticket} slots in peer-mapped windows (other GPUs' HBM over NVLink,
+// or our own): one aligned v2 access = one transaction, so value and ticket arrive together.
+__device__ __forceinline__ void st_slot_sys(uint2 *p, uint2 v) {
+    asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1, %2};" ::"l"(p), "r"(v.x), "r"(v.y) : "memory");
+}
+__device__ __forceinline__ uint2 ld_slot_sys(const uint2 *p) {
+    uint2 v;
+    asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p) : "memory");
+    return v;
+}
 
 __device__ __forceinline__ unsigned smem_addr(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
 
@@ -379,35 +384,33 @@ toy_step_kernel(const __grid_constant__ JobList jl) {
         if (job.world > 1 && mode == DDPB_MODE_STEP) {
             // ---- one-shot all-reduce over NVLink, fused into the step (no NCCL launch, no second
             // kernel): slice c of every rank's bucket meets in every rank's receive window.
+            // Every element travels as one 8-byte {value, ticket} store (the low-latency protocol:
+            // data and "it has arrived" in a single NVLink transaction, so no fence, no flag round
+            // trip); the receiver polls its own window until the ticket of this step shows up.
             // DDP's arithmetic: scale by 1/W first, then sum (default_hooks.py:24-29); ranks are
             // summed in ascending order on every GPU, so replicas stay bit-identical.
-            const unsigned xseq = (unsigned)seq + 1u;                        // this exchange's ticket
-            const int par = (int)(seq & 1);                                  // double-buffered windows
+            const unsigned xseq = (unsigned)seq + 1u;                        // this exchange's ticket (never 0)
+            const int par = (int)(seq & 1);                                  // double-buffered: a peer is at most one step ahead
             const int W = job.world, me = job.rank;
-            const float contrib = (own < P) ? __fmul_rn(total, job.inv_world) : total;
             if (owner) {
+                const float contrib = (own < P) ? __fmul_rn(total, job.inv_world) : total;
                 const size_t at = (size_t)(par * DDPB_MAX_PEERS + me) * kXchgRow + own;
-                for (int dst = 0; dst < W; ++dst) st_relaxed_sys(jref.peer_data[dst] + at, contrib);
-                __threadfence_system();
-            }
-            optimizer_barrier();
-            if (slot < W)                                                    // publish: one flag per destination
-                st_release_sys(jref.peer_flags[slot] + (par * DDPB_MAX_PEERS + me) * kCluster + cta, xseq);
-            if (slot < W) {                                                  // wait for rank `slot`'s slice
-                const unsigned *flag = jref.peer_flags[me] + (par * DDPB_MAX_PEERS + slot) * kCluster + cta;
-                long long spins = 0;
-                while (ld_acquire_sys(flag) != xseq) {
-                    if (++spins > (1ll << 26)) {                             // ~1 s: a peer died; fail loudly, do not hang
-                        job.state->reserved[0] = 1;
-                        break;
-                    }
-                }
-            }
-            optimizer_barrier();
-            if (owner) {
+                for (int dst = 0; dst < W; ++dst)
+                    st_slot_sys(reinterpret_cast<uint2 *>(jref.peer_data[dst]) + at, make_uint2(__float_as_uint(contrib), xseq));
                 total = 0.f;
-                const float *mine = jref.peer_data[me] + (size_t)(par * DDPB_MAX_PEERS) * kXchgRow + own;
-                for (int src = 0; src < W; ++src) total += ld_relaxed_sys(mine + (size_t)src * kXchgRow);
+                const uint2 *mine = reinterpret_cast<const uint2 *>(jref.peer_data[me]) + (size_t)(par * DDPB_MAX_PEERS) * kXchgRow + own;
+                for (int src = 0; src < W; ++src) {
+                    uint2 got = ld_slot_sys(mine + (size_t)src * kXchgRow);
+                    long long spins = 0;
+                    while (got.y != xseq) {
+                        if (++spins > (1ll << 26)) {                         // ~1 s: a peer died; fail loudly, do not hang
+                            job.state->reserved[0] = 1;
+                            break;
+                        }
+                        got = ld_slot_sys(mine + (size_t)src * kXchgRow);
+                    }
+                    total += __uint_as_float(got.x);
+                }
             }
         }
         if (owner) {
@@ -610,7 +613,7 @@ static int launch_toy_step(const ddpb_toy_job *jobs, int njobs, cudaStream_t str
             DDPB_REQUIRE(q.world <= DDPB_MAX_PEERS && q.rank >= 0 && q.rank < q.world,
                          "ddpb_toy_step: job %d: world %d / rank %d outside the %d-peer exchange", j, q.world, q.rank, DDPB_MAX_PEERS);
             for (int r = 0; r < q.world; ++r)
-                DDPB_REQUIRE(q.peer_data[r] && q.peer_flags[r], "ddpb_toy_step: job %d: peer window %d not mapped", j, r);
+                DDPB_REQUIRE(q.peer_data[r] && ((uintptr_t)q.peer_data[r] & 7) == 0, "ddpb_toy_step: job %d: peer window %d not mapped", j, r);
         }
         jl.jobs[j] = q;
         // the shared-memory staging of a small dataset needs whole, aligned float4 rows
@@ -642,24 +645,24 @@ DDPB_API int ddpb_toy_step_h2d(const ddpb_toy_job *jobs, int njobs, void *dst_de
 // memory pool at start-up (a raw cudaMalloc would fail or fragment that pool), a
 // latency-critical loop that must never take the allocator's device-wide synchronisation, a
 // test rig that wants the multi-rank arithmetic on a single-GPU box.  For them the windows
-// of up to DDPB_MAX_VIRTUAL_RANKS replicas live in the file-scope array below (96 KiB of
+// of up to DDPB_MAX_VIRTUAL_RANKS replicas live in the file-scope array below (188 KiB of
 // every GPU that loads this library, held until the process exits), and all replicas run in
 // one launch (blockIdx.y = replica), so they are co-resident by construction.
 //
 // Rules that follow from sharing one array:
-//   * It keeps whatever the previous call left.  The arrival flags are cleared on the stream
-//     at the start of every call (data rows are fully rewritten before they are read).
+//   * It keeps whatever the previous call left, including arrival tickets that could match a
+//     later caller's step number by accident, so the windows in use are cleared on the stream at
+//     the start of every call.
 //   * Two calls whose kernels overlap on the GPU (different streams, no dependency) race on
 //     the array; serialise them.
 //   * The device address of the array is looked up once per device, on the first call made
 //     with that device current; make that first call before any stream capture begins.
 namespace {
 
-constexpr size_t kWindowDataBytes = sizeof(float) * DDPB_XCHG_DATA_FLOATS;
-constexpr size_t kWindowFlagBytes = sizeof(uint32_t) * DDPB_XCHG_FLAG_WORDS;
-constexpr size_t kVirtualBytes = DDPB_MAX_VIRTUAL_RANKS * (kWindowDataBytes + kWindowFlagBytes);
+constexpr size_t kWindowBytes = DDPB_XCHG_WINDOW_BYTES;
+constexpr size_t kVirtualBytes = DDPB_MAX_VIRTUAL_RANKS * kWindowBytes;
 
-// layout: [rank 0 data][rank 1 data]...[rank 0 flags][rank 1 flags]...
+// layout: [rank 0 window][rank 1 window]...
 static __device__ __align__(256) unsigned char g_virtual_windows[kVirtualBytes];
 
 // In host code `g_virtual_windows` is only a handle for the runtime, never an address a kernel
@@ -688,7 +691,6 @@ DDPB_API int ddpb_toy_step_virtual_ranks(const ddpb_toy_job *jobs, int nranks, v
                  "(use ddpb_toy_step with caller-provided windows beyond that)", nranks, DDPB_MAX_VIRTUAL_RANKS);
     unsigned char *base = nullptr;
     if (int rc = virtual_window_base(&base)) return rc;
-    unsigned char *flags0 = base + DDPB_MAX_VIRTUAL_RANKS * kWindowDataBytes;
     ddpb_toy_job local[DDPB_MAX_VIRTUAL_RANKS];
     for (int r = 0; r < nranks; ++r) {
         DDPB_REQUIRE(jobs[r].mode == DDPB_MODE_STEP, "ddpb_toy_step_virtual_ranks: replica %d is not in STEP mode", r);
@@ -697,10 +699,10 @@ DDPB_API int ddpb_toy_step_virtual_ranks(const ddpb_toy_job *jobs, int nranks, v
         local[r].rank = r;
         local[r].inv_world = 1.0f / (float)nranks;
         for (int p = 0; p < DDPB_MAX_PEERS; ++p) {
-            local[r].peer_data[p] = p < nranks ? reinterpret_cast<float *>(base + p * kWindowDataBytes) : nullptr;
-            local[r].peer_flags[p] = p < nranks ? reinterpret_cast<uint32_t *>(flags0 + p * kWindowFlagBytes) : nullptr;
+            local[r].peer_data[p] = p < nranks ? reinterpret_cast<float *>(base + p * kWindowBytes) : nullptr;
+            local[r].peer_flags[p] = nullptr;
         }
     }
-    DDPB_CUDA(cudaMemsetAsync(flags0, 0, nranks * kWindowFlagBytes, (cudaStream_t)stream));
+    DDPB_CUDA(cudaMemsetAsync(base, 0, nranks * kWindowBytes, (cudaStream_t)stream));     // stale tickets must not match
     return launch_toy_step(local, nranks, (cudaStream_t)stream);
 }

@@ -208,10 +208,10 @@ class ToyBackend:
         if self.world > _lib.MAX_PEERS:
             return
         lib = self.engine.lib
-        data_bytes, flag_bytes = _lib.XCHG_DATA_FLOATS * 4, _lib.XCHG_FLAG_WORDS * 4
+        window_bytes = _lib.XCHG_WINDOW_BYTES
         mine, handle = ctypes.c_void_p(), ctypes.create_string_buffer(64)
         with torch.cuda.device(self.device):
-            _lib.check(lib.ddpb_peer_alloc(data_bytes + flag_bytes, ctypes.byref(mine), handle), "ddpb_peer_alloc")
+            _lib.check(lib.ddpb_peer_alloc(window_bytes, ctypes.byref(mine), handle), "ddpb_peer_alloc")
             import socket
             handles = [None] * self.world
             dist.all_gather_object(handles, (socket.gethostname(), handle.raw), group=self.process_group)
@@ -239,7 +239,6 @@ class ToyBackend:
         j = self.job
         for r, ptr in enumerate(mapped):
             j.peer_data[r] = ptr
-            j.peer_flags[r] = ptr + data_bytes
         j.world, j.rank, j.inv_world = self.world, self.rank, 1.0 / self.world
         self.fused_exchange = True
         self.lazy = True

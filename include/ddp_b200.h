@@ -31,9 +31,8 @@ extern "C" {
 #define DDPB_TOY_PARAMS 371        /* 3H^2 + 7H + 1 */
 #define DDPB_MAX_JOBS 4            /* models per ddpb_toy_step launch */
 #define DDPB_MAX_PEERS 8           /* GPUs of one NVSwitch box taking part in the fused exchange */
-#define DDPB_XCHG_ROW 376          /* floats per (parity, source rank) row of a peer window (372 used) */
-#define DDPB_XCHG_DATA_FLOATS (2 * DDPB_MAX_PEERS * DDPB_XCHG_ROW)   /* one model's data window */
-#define DDPB_XCHG_FLAG_WORDS (2 * DDPB_MAX_PEERS * 8)                /* one model's flag window */
+#define DDPB_XCHG_ROW 376          /* 8-byte {value, ticket} slots per (parity, source rank) row (372 used) */
+#define DDPB_XCHG_WINDOW_BYTES (2 * DDPB_MAX_PEERS * DDPB_XCHG_ROW * 8)   /* one model's window per rank: 48 128 B */
 
 /* ---- introspection ------------------------------------------------------- */
 int ddpb_version(void);
@@ -118,10 +117,10 @@ typedef struct ddpb_toy_job {
     double lr, beta1, beta2, eps, momentum;
     /* world > 1 with DDPB_MODE_STEP: the gradient all-reduce (demo.py:107,109 via the c10d reducer)
      * is fused into the step as a one-shot exchange over peer-mapped windows (NVLink P2P stores):
-     * peer_data[r] / peer_flags[r] are rank r's windows as mapped into THIS process
-     * (ddpb_peer_alloc / ddpb_peer_open), zero-initialised, DDPB_XCHG_DATA_FLOATS floats and
-     * DDPB_XCHG_FLAG_WORDS words each; entry [rank] is this rank's own window.  state->seq must
-     * advance in lock step on all ranks; state->reserved[0] != 0 afterwards = a peer timed out. */
+     * peer_data[r] is rank r's window as mapped into THIS process (ddpb_peer_alloc /
+     * ddpb_peer_open), zero-initialised, DDPB_XCHG_WINDOW_BYTES bytes, 8-byte aligned; entry [rank]
+     * is this rank's own window.  state->seq must advance in lock step on all ranks;
+     * state->reserved[0] != 0 afterwards = a peer timed out.  peer_flags is unused (reserved). */
     float *peer_data[DDPB_MAX_PEERS];
     uint32_t *peer_flags[DDPB_MAX_PEERS];
     int32_t world, rank;
@@ -140,11 +139,11 @@ int ddpb_toy_step_h2d(const ddpb_toy_job *jobs, int njobs, void *dst_dev, const 
  * r's job (DDPB_MODE_STEP, its own params/m/v/grads/state and its own batch; all replicas'
  * state->seq must be equal).  Unlike ddpb_toy_step with world > 1, the caller provides no
  * exchange windows and nothing is allocated, by this call or ever: the windows are a
- * 96 KiB array compiled into the library (every GPU that loads it holds one until exit).
+ * 188 KiB array compiled into the library (every GPU that loads it holds one until exit).
  * It is meant for callers that cannot allocate device memory themselves -- the device was
  * handed to another pool, or the loop must not take the allocator's device-wide sync.
  * world/rank/inv_world/peer_* of the jobs are ignored and filled in here.
- * The array is shared by every call and keeps the previous call's contents: the arrival flags
+ * The array is shared by every call and keeps the previous call's contents: the windows in use
  * are cleared on `stream` first, and calls whose kernels overlap on the GPU race -- serialise
  * them.  The first call on each device looks the array's device address up; make that call
  * before starting any stream capture.  More than DDPB_MAX_VIRTUAL_RANKS replicas is an error. */

@@ -29,8 +29,8 @@ def _replicas(init, windows=None):
         if windows is not None:                      # existing entry point: caller-allocated exchange windows
             j = h.job
             j.world, j.rank, j.inv_world = 2, r, 0.5
-            for p, (data, flags) in enumerate(windows):
-                j.peer_data[p], j.peer_flags[p] = data.data_ptr(), flags.data_ptr()
+            for p, window in enumerate(windows):
+                j.peer_data[p] = window.data_ptr()
     return reps
 
 
@@ -47,8 +47,7 @@ def test_two_steps_match_the_allocating_entry_point(oracle, native_lib, golden_d
     g = np.load(os.path.join(golden_dir, "ref_w2.npz"))
     d = np.load(os.path.join(golden_dir, "dataset.npz"))
     X, Y = dev(d["x"]), dev(d["y"])
-    windows = [(torch.zeros(_lib.XCHG_DATA_FLOATS, device="cuda"),
-                torch.zeros(_lib.XCHG_FLAG_WORDS, dtype=torch.int32, device="cuda")) for _ in range(2)]
+    windows = [torch.zeros(_lib.XCHG_WINDOW_BYTES // 4, dtype=torch.int32, device="cuda") for _ in range(2)]
     old = _replicas(g["init_X"], windows)
     new = _replicas(g["init_X"])
     p, m, v = g["init_X"].copy(), np.zeros(P, np.float32), np.zeros(P, np.float32)
