@@ -18,10 +18,10 @@
 //             epilogue: store dW straight into the flat gradient bucket; the operand row
 //             n = Hin is a row of ones, which makes column Hin of the product the bias gradient
 //
-// CTAs that compute neighbouring n-tiles of the same m-tile form a cluster of 4 (2, 1): each loads a
-// quarter of the shared A slab and TMA-multicasts it to all four, and a stage is released by
-// tcgen05.commit multicast to every CTA that filled part of it -- the A slab crosses L2 once
-// per cluster instead of once per tile (the kernels were L2-bound without it, profiles/).
+// Optional (DDPB_GEMM_CLUSTER=2|4): CTAs that compute neighbouring n-tiles of the same m-tile form a
+// cluster, each loads its share of the common A slab and TMA-multicasts it to all, and a stage is
+// released by tcgen05.commit multicast to every CTA that filled part of it.  Correct, but no
+// faster on B200 for these shapes (see cluster_width), so off by default.
 // Structure (one CTA, 256 threads): warp 0 = TMA producer, warp 1 = MMA issuer (one elected
 // thread), warp 2 = TMEM allocator, warps 4..7 = epilogue (tcgen05.ld 32 lanes x 32 columns at a
 // time).  A 6-stage ring of {A tile, B tile} (32 KB per stage, 128-byte swizzle) is filled by
@@ -379,13 +379,16 @@ int launch(const CUtensorMap &ma, const CUtensorMap &mb, const EpiParams &ep, in
     return 0;
 }
 
-// Cluster width for the multicast of the shared A slab (DDPB_GEMM_CLUSTER = 1, 2 or 4; default 4).
+// Cluster width for the multicast of the shared A slab (DDPB_GEMM_CLUSTER = 1, 2 or 4).  Default 1:
+// measured on B200, multicast does not help these shapes -- the kernels are bound by how fast ONE
+// SM can ingest operand tiles into shared memory (~95 GB/s/SM, 0.26 us per 24-32 KB k-block whether
+// the A slab arrives by multicast or not), not by L2 output bandwidth.
 int cluster_width() {
     static int w = 0;
     if (!w) {
         const char *e = getenv("DDPB_GEMM_CLUSTER");
-        w = e ? atoi(e) : 4;
-        if (w != 1 && w != 2 && w != 4) w = 4;
+        w = e ? atoi(e) : 1;
+        if (w != 1 && w != 2 && w != 4) w = 1;
     }
     return w;
 }
