@@ -90,3 +90,51 @@ def test_mpiexec_entry_point_with_the_compat_launcher(tmp_path, golden_dir):
     mean = np.mean([r["losses"] for r in ranks], axis=0)          # equal shards: mean of local losses = logged value
     ref = np.stack([g["lossX"], g["lossY"]], axis=1)[:200]
     assert np.max(np.abs(mean - ref) / ref) <= 2e-5
+
+
+@pytest.mark.parametrize("cap_mb", [25, 0.05])
+def test_widened_model_data_parallel(tmp_path, cap_mb):
+    """Widened model on 2 GPUs: rank 0's weights are broadcast, gradients are averaged bucket by
+    bucket (one bucket per layer at 25 MiB, many at 0.05 MiB), replicas stay bit-identical, and the
+    run tracks an fp32 PyTorch model trained on the concatenated batch (equal shards: the average
+    of the shard gradients IS the gradient of the whole batch) within the tf32 tolerance."""
+    if 2 not in _worlds():
+        pytest.skip("needs 2 GPUs")
+    H, B, steps = 128, 64, 12
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+           "--master-port", str(_free_port()), os.path.join(ROOT, "tests", "_wide_worker.py"), str(tmp_path), str(H),
+           str(B), str(steps), str(cap_mb)]
+    proc = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=600, env=dict(os.environ, OMP_NUM_THREADS="1"))
+    assert proc.returncode == 0, (proc.stdout + proc.stderr)[-4000:]
+    r0, r1 = (np.load(os.path.join(tmp_path, f"rank{r}.npz")) for r in range(2))
+    assert np.array_equal(r0["init"], r1["init"])                       # broadcast from rank 0
+    assert np.array_equal(r0["final"], r1["final"])                     # replicas stay identical
+    assert int(r0["buckets"]) == (5 if cap_mb == 25 else 8)          # 16512-float hidden layers cut at 13104 floats
+    # fp32 reference on the concatenated batch
+    torch.backends.cuda.matmul.allow_tf32 = False
+    dims = (2, H, H, H, H, 1)
+    layers = []
+    for i in range(5):
+        layers.append(torch.nn.Linear(dims[i], dims[i + 1]))
+        if i < 4:
+            layers.append(torch.nn.LeakyReLU())
+    twin = torch.nn.Sequential(*layers).cuda()
+    flat, off = torch.from_numpy(r0["init"]).cuda(), 0
+    with torch.no_grad():
+        for p in twin.parameters():
+            p.copy_(flat[off:off + p.numel()].view_as(p)); off += p.numel()
+    opt = torch.optim.Adam(twin.parameters(), lr=1e-3)
+    g = torch.Generator().manual_seed(7)
+    for step in range(steps):
+        z = torch.randn(2 * B, generator=g)
+        y = (0.5 * torch.randn(2 * B, generator=g) + z * z).view(-1, 1).cuda()
+        x = torch.stack([z, z], 1).cuda()
+        opt.zero_grad()
+        per_sample = (twin(x) - y) ** 2
+        per_sample.mean().backward()
+        opt.step()
+        shard = [per_sample[r * B:(r + 1) * B].mean().item() for r in range(2)]
+        assert abs(r0["losses"][step] - shard[0]) <= 2e-2 * shard[0] and abs(r1["losses"][step] - shard[1]) <= 2e-2 * shard[1]
+    final_t = torch.cat([p.detach().reshape(-1) for p in twin.parameters()]).cpu().numpy()
+    delta = np.abs(r0["final"] - final_t)
+    assert delta.max() <= 2 * steps * 1e-3 and delta.mean() <= 5e-4
