@@ -134,7 +134,8 @@ def test_widened_model_data_parallel(tmp_path, cap_mb):
         per_sample.mean().backward()
         opt.step()
         shard = [per_sample[r * B:(r + 1) * B].mean().item() for r in range(2)]
-        assert abs(r0["losses"][step] - shard[0]) <= 2e-2 * shard[0] and abs(r1["losses"][step] - shard[1]) <= 2e-2 * shard[1]
+        tol = 4e-3 if step == 0 else 5e-2          # same weights at step 0; afterwards the two Adam runs drift apart
+        assert abs(r0["losses"][step] - shard[0]) <= tol * shard[0] and abs(r1["losses"][step] - shard[1]) <= tol * shard[1], step
     final_t = torch.cat([p.detach().reshape(-1) for p in twin.parameters()]).cpu().numpy()
     delta = np.abs(r0["final"] - final_t)
     assert delta.max() <= 2 * steps * 1e-3 and delta.mean() <= 5e-4
