@@ -219,9 +219,10 @@ class WideBackend:
             gw, gb = self._g(l)
             side.wait_stream(main)                                # dz_t[cur] is complete on the main stream
             ck(lib.ddpb_linear_wgrad(dz_t[cur].data_ptr(), act_t[l - 1].data_ptr(), gw, gb, B, H, H, ld, side.cuda_stream), "wgrad")
-            self._layer_done(l, with_update, side)
             ck(lib.ddpb_linear_dgrad(dz[cur].data_ptr(), w, act[l - 1].data_ptr(), dz[cur + 1].data_ptr(),
                                      dz_t[cur + 1].data_ptr(), B, H, H, ld, stream), "dgrad")
+            # the bucket's update overwrites W_l: it must follow wgrad (side) AND dgrad, which reads W_l (main)
+            self._layer_done(l, with_update, side)
             cur += 1
             eng.launches += 2
         gw, gb = self._g(0)
@@ -244,7 +245,9 @@ class WideBackend:
             return
         if layer == 4:
             self.sgd_steps += int(with_update)
-        self.comm_stream.wait_stream(produced_on if produced_on is not None else torch.cuda.current_stream(self.device))
+        self.comm_stream.wait_stream(torch.cuda.current_stream(self.device))
+        if produced_on is not None:
+            self.comm_stream.wait_stream(produced_on)
         cs = self.comm_stream.cuda_stream
         mine = [bk for bk in self.buckets if bk[0] == layer]
         for _, start, n in mine:
