@@ -87,6 +87,10 @@ __device__ __forceinline__ void tma_load_2d(unsigned dst, const CUtensorMap *map
         "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
         ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1) : "memory");
 }
+// Ask L2 for a tile that a later TMA load will want (no shared memory involved).
+__device__ __forceinline__ void tma_prefetch_2d(const CUtensorMap *map, int c0, int c1) {
+    asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global.tile [%0, {%1, %2}];" ::"l"(map), "r"(c0), "r"(c1) : "memory");
+}
 // The same load delivered to the same shared-memory offset of every CTA in `mask` (and counted
 // on each of their mbarriers): CTAs of a cluster that need the same A slab fetch it from L2 once.
 __device__ __forceinline__ void tma_load_2d_multicast(unsigned dst, const CUtensorMap *map, unsigned bar, int c0, int c1,
@@ -214,8 +218,22 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     if (warp == 0) {
         // ===== TMA producer =====
         if (lane == 0) {
+            // The ring holds ~190 KB in flight per SM; at ~2 us of loaded HBM latency that is only
+            // ~95 GB/s per SM (measured: 0.26 us per k-block whatever its size).  The weight tiles
+            // (the operand that really comes from HBM) are therefore requested into L2 kPrefetch
+            // k-blocks ahead of the loads that consume them, which then see L2 latency instead.
+            constexpr int kPrefetch = EPI == EPI_WGRAD ? 0 : 32;
+            auto prefetch_b = [&](int kbp) {
+                if (kPrefetch == 0 || kbp >= num_k) return;
+                if (!B_MN) tma_prefetch_2d(&map_b, kbp * BK, n0);
+                else
+#pragma unroll
+                    for (int a = 0; a < BN / 32; ++a) tma_prefetch_2d(&map_b, n0 + a * 32, kbp * BK);
+            };
+            for (int kbp = 0; kbp < kPrefetch; ++kbp) prefetch_b(kbp);
             for (int kb = 0; kb < num_k; ++kb) {
                 const int s = kb % kStages;
+                prefetch_b(kb + kPrefetch);
                 if (kb >= kStages) mbar_wait(saddr(&bars[kStages + s]), ((kb / kStages) - 1) & 1);
                 const unsigned full = saddr(&bars[s]);
                 const unsigned a_dst = saddr(smem + s * kStageBytes), b_dst = a_dst + kATileBytes;
