@@ -18,10 +18,15 @@
 //             epilogue: store dW straight into the flat gradient bucket; the operand row
 //             n = Hin is a row of ones, which makes column Hin of the product the bias gradient
 //
-// Optional (DDPB_GEMM_CLUSTER=2|4): CTAs that compute neighbouring n-tiles of the same m-tile form a
-// cluster, each loads its share of the common A slab and TMA-multicasts it to all, and a stage is
-// released by tcgen05.commit multicast to every CTA that filled part of it.  Correct, but no
-// faster on B200 for these shapes (see cluster_width), so off by default.
+// Measured (tools/gemm_timeline.py, clock64 stamps in the MMA thread): a CTA retires one 32-wide
+// k-block every ~490 cycles = four 128x128x8 tf32 MMAs at ~123 cycles each, i.e. the tensor pipe of
+// an SM that has a tile is saturated (1024 tf32 MAC/clk/SM); data always lands ~3500 cycles after it
+// was requested and the 6-stage ring hides that.  Tiles larger, multicast of the shared A slab and
+// L2 prefetch of the weight tiles were all tried and change nothing, because the bound is not
+// memory.  What was wrong at B <= 256 was the NUMBER of tiles: 2 x H/128 (64 at H = 4096) for 148
+// SMs.  So the K loop is split across a cluster of SPLIT CTAs (blockIdx.z): ranks > 0 park their
+// partial accumulator in their own shared memory, rank 0 adds them through distributed shared
+// memory in its epilogue.
 // Structure (one CTA, 256 threads): warp 0 = TMA producer, warp 1 = MMA issuer (one elected
 // thread), warp 2 = TMEM allocator, warps 4..7 = epilogue (tcgen05.ld 32 lanes x 32 columns at a
 // time).  A 6-stage ring of {A tile, B tile} (32 KB per stage, 128-byte swizzle) is filled by
@@ -52,6 +57,14 @@ template <int BN> struct Cfg {
 };
 
 enum { EPI_FWD = 0, EPI_DGRAD = 1, EPI_WGRAD = 2 };
+
+#ifdef DDPB_GEMM_TIMELINE
+// Development aid (tools/gemm_timeline.py): clock64 stamps of CTA (0,0)'s producer and MMA threads.
+__device__ long long g_gemm_stamps[3][512];
+#define GEMM_STAMP(row, i) do { if (blockIdx.x == 0 && blockIdx.y == 0 && (i) < 512) g_gemm_stamps[row][i] = clock64(); } while (0)
+#else
+#define GEMM_STAMP(row, i) do { } while (0)
+#endif
 
 struct EpiParams {
     const float *bias;        // FWD: [N]
@@ -87,23 +100,6 @@ __device__ __forceinline__ void tma_load_2d(unsigned dst, const CUtensorMap *map
         "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
         ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1) : "memory");
 }
-// Ask L2 for a tile that a later TMA load will want (no shared memory involved).
-__device__ __forceinline__ void tma_prefetch_2d(const CUtensorMap *map, int c0, int c1) {
-    asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global.tile [%0, {%1, %2}];" ::"l"(map), "r"(c0), "r"(c1) : "memory");
-}
-// The same load delivered to the same shared-memory offset of every CTA in `mask` (and counted
-// on each of their mbarriers): CTAs of a cluster that need the same A slab fetch it from L2 once.
-__device__ __forceinline__ void tma_load_2d_multicast(unsigned dst, const CUtensorMap *map, unsigned bar, int c0, int c1,
-                                                      unsigned short mask) {
-    asm volatile(
-        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster "
-        "[%0], [%1, {%3, %4}], [%2], %5;"
-        ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "h"(mask) : "memory");
-}
-__device__ __forceinline__ void umma_commit_multicast(unsigned bar, unsigned short mask) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
-                 ::"r"(bar), "h"(mask) : "memory");
-}
 __device__ __forceinline__ unsigned cluster_ctarank() {
     unsigned r;
     asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
@@ -112,6 +108,13 @@ __device__ __forceinline__ unsigned cluster_ctarank() {
 __device__ __forceinline__ void cluster_sync_all() {
     asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
     asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ float ld_dsmem_f32(const float *local, unsigned rank) {
+    unsigned remote;
+    float v;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(saddr(local)), "r"(rank));
+    asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(remote) : "memory");
+    return v;
 }
 __device__ __forceinline__ void tmem_alloc(unsigned slot_smem, unsigned cols) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(slot_smem), "r"(cols) : "memory");
@@ -178,7 +181,7 @@ __device__ __forceinline__ unsigned make_idesc(bool b_mn_major) {
     return d;
 }
 
-template <int EPI, bool B_MN, int BN, int CL>
+template <int EPI, bool B_MN, int BN, int SPLIT>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                  const EpiParams ep, int M, int N, int K) {
@@ -194,14 +197,13 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     const int n0 = blockIdx.x * BN, m0 = blockIdx.y * BM;
     const int num_k = (K + BK - 1) / BK;
 
-    // CL > 1: the CL CTAs of a cluster compute CL neighbouring n-tiles of the same m-tile; each loads
-    // 1/CL of the shared A slab and multicasts it, so a stage is free only when all CL have used it.
-    const unsigned crank = CL > 1 ? cluster_ctarank() : 0u;
-    constexpr unsigned short kMask = (unsigned short)((1u << CL) - 1u);
+    // SPLIT > 1: the SPLIT CTAs of a cluster (blockIdx.z) share one output tile and split its K loop.
+    const unsigned krank = SPLIT > 1 ? cluster_ctarank() : 0u;
+    const int kb_begin = (int)((long long)num_k * krank / SPLIT), kb_count = (int)((long long)num_k * (krank + 1) / SPLIT) - kb_begin;
     if (threadIdx.x == 0) {
         for (int s = 0; s < kStages; ++s) {
             mbar_init(saddr(&bars[s]), 1);
-            mbar_init(saddr(&bars[kStages + s]), CL);
+            mbar_init(saddr(&bars[kStages + s]), 1);
         }
         mbar_init(saddr(&bars[2 * kStages]), 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -211,45 +213,25 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     if (warp == 2) tmem_alloc(saddr(tmem_slot), kTmemCols);
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
-    if (CL > 1) cluster_sync_all();                    // peers' barriers exist before anything is multicast
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const unsigned tmem_base = *tmem_slot;
 
     if (warp == 0) {
         // ===== TMA producer =====
         if (lane == 0) {
-            // The ring holds ~190 KB in flight per SM; at ~2 us of loaded HBM latency that is only
-            // ~95 GB/s per SM (measured: 0.26 us per k-block whatever its size).  The weight tiles
-            // (the operand that really comes from HBM) are therefore requested into L2 kPrefetch
-            // k-blocks ahead of the loads that consume them, which then see L2 latency instead.
-            constexpr int kPrefetch = EPI == EPI_WGRAD ? 0 : 32;
-            auto prefetch_b = [&](int kbp) {
-                if (kPrefetch == 0 || kbp >= num_k) return;
-                if (!B_MN) tma_prefetch_2d(&map_b, kbp * BK, n0);
-                else
-#pragma unroll
-                    for (int a = 0; a < BN / 32; ++a) tma_prefetch_2d(&map_b, n0 + a * 32, kbp * BK);
-            };
-            for (int kbp = 0; kbp < kPrefetch; ++kbp) prefetch_b(kbp);
-            for (int kb = 0; kb < num_k; ++kb) {
-                const int s = kb % kStages;
-                prefetch_b(kb + kPrefetch);
-                if (kb >= kStages) mbar_wait(saddr(&bars[kStages + s]), ((kb / kStages) - 1) & 1);
+            for (int it = 0; it < kb_count; ++it) {
+                const int s = it % kStages, kb = kb_begin + it;
+                if (it >= kStages) mbar_wait(saddr(&bars[kStages + s]), ((it / kStages) - 1) & 1);
                 const unsigned full = saddr(&bars[s]);
                 const unsigned a_dst = saddr(smem + s * kStageBytes), b_dst = a_dst + kATileBytes;
+                GEMM_STAMP(0, it);                                                    // producer: stage free, issuing loads
                 mbar_expect_tx(full, kStageBytes);
-                if (CL == 1) {
-                    tma_load_2d(a_dst, &map_a, full, kb * BK, m0);                   // [128 rows][32 k]
-                } else {
-                    constexpr int kSliceRows = BM / CL;                              // my share of the slab, for everyone
-                    tma_load_2d_multicast(a_dst + crank * kSliceRows * BK * 4, &map_a, full, kb * BK,
-                                          m0 + (int)crank * kSliceRows, kMask);
-                }
+                tma_load_2d(a_dst, &map_a, full, kb * BK, m0);                       // [128 rows][32 k]
                 if (!B_MN) {
-                    tma_load_2d(b_dst, &map_b, full, kb * BK, n0);                   // [128 rows][32 k]
+                    tma_load_2d(b_dst, &map_b, full, kb * BK, n0);                   // [BN rows][32 k]
                 } else {
 #pragma unroll
-                    for (int a = 0; a < BN / 32; ++a)                                // 4 boxes [32 k][32 n]
+                    for (int a = 0; a < BN / 32; ++a)                                // boxes [32 k][32 n]
                         tma_load_2d(b_dst + a * 4096, &map_b, full, n0 + a * 32, kb * BK);
                 }
             }
@@ -258,9 +240,10 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         // ===== MMA issuer (one thread) =====
         if (lane == 0) {
             const unsigned idesc = make_idesc<BN>(B_MN);
-            for (int kb = 0; kb < num_k; ++kb) {
-                const int s = kb % kStages;
-                mbar_wait(saddr(&bars[s]), (kb / kStages) & 1);
+            for (int it = 0; it < kb_count; ++it) {
+                const int s = it % kStages;
+                mbar_wait(saddr(&bars[s]), (it / kStages) & 1);
+                GEMM_STAMP(1, it);                                                    // consumer: data landed
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 const unsigned a_base = saddr(smem + s * kStageBytes), b_base = a_base + kATileBytes;
 #pragma unroll
@@ -268,23 +251,49 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
                     const unsigned long long da = make_desc(a_base + k * 32, 0, 1024, 2);
                     const unsigned long long db = B_MN ? make_desc(b_base + k * 1024, 4096, 512, 1)
                                                        : make_desc(b_base + k * 32, 0, 1024, 2);
-                    umma_tf32(tmem_base, da, db, idesc, (kb | k) != 0);
+                    umma_tf32(tmem_base, da, db, idesc, (it | k) != 0);
                 }
-                if (CL == 1) umma_commit(saddr(&bars[kStages + s]));                 // frees the stage when the MMAs retire
-                else umma_commit_multicast(saddr(&bars[kStages + s]), kMask);        // ... in every CTA that filled part of it
+                GEMM_STAMP(2, it);                                                    // consumer: MMAs issued
+                umma_commit(saddr(&bars[kStages + s]));                              // frees the stage when the MMAs retire
             }
             umma_commit(saddr(&bars[2 * kStages]));                                  // accumulator complete
         }
-    } else if (warp >= 4) {
-        // ===== epilogue: TMEM -> registers -> global =====
-        const int q = warp - 4;                                                      // TMEM lanes [32q, 32q+32)
-        const int m = m0 + q * 32 + lane;
+    }
+    // The pipeline stages are dead once the accumulator is complete: with SPLIT > 1 they become the
+    // parking area of the partial tile, laid out [column][row] so that lanes (rows) are contiguous.
+    float *park = reinterpret_cast<float *>(smem);
+    if (warp >= 4) {
         mbar_wait(saddr(&bars[2 * kStages]), 0);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        if (SPLIT > 1 && krank > 0) {
+            const int q = warp - 4;
+#pragma unroll 1
+            for (int c0 = 0; c0 < BN; c0 += 32) {
+                float v[32];
+                tmem_ld32(tmem_base + ((unsigned)(q * 32) << 16) + (unsigned)c0, v);
+#pragma unroll
+                for (int i = 0; i < 32; ++i) park[(c0 + i) * BM + q * 32 + lane] = v[i];
+            }
+        }
+    }
+    if (SPLIT > 1) {
+        __syncthreads();
+        cluster_sync_all();                                                          // partial tiles are parked
+    }
+    if (warp >= 4 && krank == 0) {
+        // ===== epilogue: TMEM (+ the other ranks' partials) -> registers -> global =====
+        const int q = warp - 4;                                                      // TMEM lanes [32q, 32q+32)
+        const int m = m0 + q * 32 + lane;
 #pragma unroll 1
         for (int c0 = 0; c0 < BN; c0 += 32) {
             float v[32];
             tmem_ld32(tmem_base + ((unsigned)(q * 32) << 16) + (unsigned)c0, v);
+            if (SPLIT > 1) {
+#pragma unroll 1
+                for (unsigned r = 1; r < (unsigned)SPLIT; ++r)
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) v[i] += ld_dsmem_f32(park + (c0 + i) * BM + q * 32 + lane, r);
+            }
             const int nb = n0 + c0;
             if (EPI == EPI_FWD) {
 #pragma unroll
@@ -333,7 +342,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     }
     __syncthreads();
-    if (CL > 1) cluster_sync_all();                    // nobody leaves while a peer may still signal its barriers
+    if (SPLIT > 1) cluster_sync_all();                 // nobody leaves while rank 0 may still read its parked tile
     if (warp == 2) {
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         tmem_dealloc(tmem_base, kTmemCols);
@@ -374,58 +383,59 @@ int make_map(CUtensorMap *map, const float *base, long long rows, long long cols
     return 0;
 }
 
-template <int EPI, bool B_MN, int BN, int CL>
+template <int EPI, bool B_MN, int BN, int SPLIT>
 int launch(const CUtensorMap &ma, const CUtensorMap &mb, const EpiParams &ep, int M, int N, int K, cudaStream_t stream) {
     static bool configured = false;
     if (!configured) {
-        DDPB_CUDA(cudaFuncSetAttribute(gemm_tf32_kernel<EPI, B_MN, BN, CL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        DDPB_CUDA(cudaFuncSetAttribute(gemm_tf32_kernel<EPI, B_MN, BN, SPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        Cfg<BN>::kSmemBytes));
         configured = true;
     }
-    const int n_tiles = (N + BN - 1) / BN;
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3((n_tiles + CL - 1) / CL * CL, (M + BM - 1) / BM, 1);   // whole clusters; surplus tiles only feed their peers
+    cfg.gridDim = dim3((N + BN - 1) / BN, (M + BM - 1) / BM, SPLIT);
     cfg.blockDim = dim3(kThreads);
     cfg.dynamicSmemBytes = Cfg<BN>::kSmemBytes;
     cfg.stream = stream;
     cudaLaunchAttribute attr;
     attr.id = cudaLaunchAttributeClusterDimension;
-    attr.val.clusterDim.x = CL; attr.val.clusterDim.y = 1; attr.val.clusterDim.z = 1;
+    attr.val.clusterDim.x = 1; attr.val.clusterDim.y = 1; attr.val.clusterDim.z = SPLIT;
     cfg.attrs = &attr;
     cfg.numAttrs = 1;
-    DDPB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tf32_kernel<EPI, B_MN, BN, CL>, ma, mb, ep, M, N, K));
+    DDPB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tf32_kernel<EPI, B_MN, BN, SPLIT>, ma, mb, ep, M, N, K));
     return 0;
 }
 
-// Cluster width for the multicast of the shared A slab (DDPB_GEMM_CLUSTER = 1, 2 or 4).  Default 1:
-// measured on B200, multicast does not help these shapes -- the kernels are bound by how fast ONE
-// SM can ingest operand tiles into shared memory (~95 GB/s/SM, 0.26 us per 24-32 KB k-block whether
-// the A slab arrives by multicast or not), not by L2 output bandwidth.
-int cluster_width() {
-    static int w = 0;
-    if (!w) {
-        const char *e = getenv("DDPB_GEMM_CLUSTER");
-        w = e ? atoi(e) : 1;
-        if (w != 1 && w != 2 && w != 4) w = 1;
+// How many ways to split K so that about one wave of 148 SMs has a tile (DDPB_GEMM_SPLIT overrides).
+int split_for(int M, int N, int K) {
+    static int forced = -1;
+    if (forced < 0) {
+        const char *e = getenv("DDPB_GEMM_SPLIT");
+        forced = e ? atoi(e) : 0;
     }
-    return w;
+    const long long tiles = (long long)((M + BM - 1) / BM) * ((N + 127) / 128);
+    int s = forced ? forced : (tiles >= 100 ? 1 : tiles >= 50 ? 2 : 4);
+    if (s != 1 && s != 2 && s != 4) s = 1;
+    while (s > 1 && (K + BK - 1) / BK < 4 * s) s >>= 1;       // keep a few k-blocks per rank
+    return s;
 }
 
-template <int EPI, bool B_MN, int BN>
-int launch_cl(const CUtensorMap &ma1, const CUtensorMap &ma2, const CUtensorMap &ma4, const CUtensorMap &mb,
-              const EpiParams &ep, int M, int N, int K, cudaStream_t stream) {
-    switch (cluster_width()) {
-        case 1: return launch<EPI, B_MN, BN, 1>(ma1, mb, ep, M, N, K, stream);
-        case 2: return launch<EPI, B_MN, BN, 2>(ma2, mb, ep, M, N, K, stream);
-        default: return launch<EPI, B_MN, BN, 4>(ma4, mb, ep, M, N, K, stream);
+template <int EPI, bool B_MN>
+int launch_split(const CUtensorMap &ma, const CUtensorMap &mb, const EpiParams &ep, int M, int N, int K, cudaStream_t stream) {
+    switch (split_for(M, N, K)) {
+        case 4: return launch<EPI, B_MN, 128, 4>(ma, mb, ep, M, N, K, stream);
+        case 2: return launch<EPI, B_MN, 128, 2>(ma, mb, ep, M, N, K, stream);
+        default: return launch<EPI, B_MN, 128, 1>(ma, mb, ep, M, N, K, stream);
     }
 }
-
-// 64-wide tiles when 128-wide ones would occupy fewer than ~3/4 of the SMs (weights are streamed
-// once either way; more CTAs = more TMA streams in flight).
-bool narrow_tiles(int M, int N) { return (long long)((M + BM - 1) / BM) * ((N + 127) / 128) < 112; }
 
 }  // namespace
+
+#ifdef DDPB_GEMM_TIMELINE
+DDPB_API int ddpb_gemm_stamps(long long *host_out /* [3*512] */) {
+    DDPB_CUDA(cudaMemcpyFromSymbol(host_out, g_gemm_stamps, sizeof(long long) * 3 * 512));
+    return 0;
+}
+#endif
 
 DDPB_API int ddpb_linear_fwd(const float *act_in, const float *W, const float *bias, float *act_out, float *act_out_t,
                              int B, int Hin, int Hout, int ld_t, int apply_act, void *stream) {
@@ -433,12 +443,10 @@ DDPB_API int ddpb_linear_fwd(const float *act_in, const float *W, const float *b
                  "ddpb_linear_fwd: bad arguments (B=%d Hin=%d Hout=%d)", B, Hin, Hout);
     DDPB_REQUIRE(!act_out_t || ld_t >= B, "ddpb_linear_fwd: transposed pitch %d < batch %d", ld_t, B);
     CUtensorMap ma, mb;
-    if (int rc = make_map(&ma, act_in, B, Hin, Hin, BM / cluster_width(), BK)) return rc;
-    const bool narrow = narrow_tiles(B, Hout);
-    if (int rc = make_map(&mb, W, Hout, Hin, Hin, narrow ? 64 : 128, BK)) return rc;
+    if (int rc = make_map(&ma, act_in, B, Hin, Hin, BM, BK)) return rc;
+    if (int rc = make_map(&mb, W, Hout, Hin, Hin, 128, BK)) return rc;
     EpiParams ep = {bias, nullptr, act_out, act_out_t, Hout, ld_t, apply_act, 0};
-    return narrow ? launch_cl<EPI_FWD, false, 64>(ma, ma, ma, mb, ep, B, Hout, Hin, (cudaStream_t)stream)
-                  : launch_cl<EPI_FWD, false, 128>(ma, ma, ma, mb, ep, B, Hout, Hin, (cudaStream_t)stream);
+    return launch_split<EPI_FWD, false>(ma, mb, ep, B, Hout, Hin, (cudaStream_t)stream);
 }
 
 DDPB_API int ddpb_linear_dgrad(const float *dz, const float *W, const float *act_prev, float *dz_prev, float *dz_prev_t,
@@ -447,11 +455,10 @@ DDPB_API int ddpb_linear_dgrad(const float *dz, const float *W, const float *act
                  "ddpb_linear_dgrad: bad arguments (B=%d Hin=%d Hout=%d)", B, Hin, Hout);
     DDPB_REQUIRE(!dz_prev_t || ld_t >= B, "ddpb_linear_dgrad: transposed pitch %d < batch %d", ld_t, B);
     CUtensorMap ma, mb;
-    if (int rc = make_map(&ma, dz, B, Hout, Hout, BM / cluster_width(), BK)) return rc;   // A: [m = sample][k = out neuron]
+    if (int rc = make_map(&ma, dz, B, Hout, Hout, BM, BK)) return rc;                 // A: [m = sample][k = out neuron]
     if (int rc = make_map(&mb, W, Hout, Hin, Hin, BK, 32, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B)) return rc;   // B: boxes [32 k][32 n], n contiguous
     EpiParams ep = {nullptr, act_prev, dz_prev, dz_prev_t, Hin, ld_t, 0, 0};
-    return narrow_tiles(B, Hin) ? launch_cl<EPI_DGRAD, true, 64>(ma, ma, ma, mb, ep, B, Hin, Hout, (cudaStream_t)stream)
-                                : launch_cl<EPI_DGRAD, true, 128>(ma, ma, ma, mb, ep, B, Hin, Hout, (cudaStream_t)stream);
+    return launch_split<EPI_DGRAD, true>(ma, mb, ep, B, Hin, Hout, (cudaStream_t)stream);
 }
 
 DDPB_API int ddpb_linear_wgrad(const float *dz_t, const float *act_t_ext, float *dW, float *db, int B, int Hin, int Hout,
@@ -459,8 +466,8 @@ DDPB_API int ddpb_linear_wgrad(const float *dz_t, const float *act_t_ext, float 
     DDPB_REQUIRE(dz_t && act_t_ext && dW && db && B >= 1 && Hin >= 32 && Hout >= 32 && Hin % 4 == 0 && ld_t % 4 == 0 && ld_t >= B,
                  "ddpb_linear_wgrad: bad arguments (B=%d Hin=%d Hout=%d ld_t=%d)", B, Hin, Hout, ld_t);
     CUtensorMap ma, mb;
-    if (int rc = make_map(&ma, dz_t, Hout, B, ld_t, BM / cluster_width(), BK)) return rc;   // A: [m = out neuron][k = sample]
+    if (int rc = make_map(&ma, dz_t, Hout, B, ld_t, BM, BK)) return rc;               // A: [m = out neuron][k = sample]
     if (int rc = make_map(&mb, act_t_ext, Hin + 1, B, ld_t, 128, BK)) return rc;      // B: [n = in neuron | ones][k = sample]
     EpiParams ep = {nullptr, nullptr, dW, db, Hin, 0, 0, Hin};
-    return launch_cl<EPI_WGRAD, false, 128>(ma, ma, ma, mb, ep, Hout, Hin + 1, B, (cudaStream_t)stream);
+    return launch<EPI_WGRAD, false, 128, 1>(ma, mb, ep, Hout, Hin + 1, B, (cudaStream_t)stream);
 }
