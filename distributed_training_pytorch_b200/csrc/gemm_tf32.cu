@@ -46,34 +46,46 @@ constexpr int kThreads = 256;
 constexpr int kATileBytes = BM * BK * 4;             // 16 KB
 constexpr float kSlope = 0.01f;
 
-// Tile configuration by output-tile width BN (128, or 64 when 128-wide tiles would leave most of
-// the 148 SMs without a CTA): bytes per pipeline stage, ring depth, dynamic shared memory.
-template <int BN> struct Cfg {
+enum { EPI_FWD = 0, EPI_DGRAD = 1, EPI_WGRAD = 2 };
+
+// Tile configuration: bytes per pipeline stage, ring depth, dynamic shared memory.  Forward and dgrad
+// stream a long K (= H) through a 6-stage ring, one CTA per SM.  Wgrad has K = B (8 k-blocks at
+// B = 256) and thousands of tiles: a 3-stage ring lets two CTAs share an SM, so that one CTA's
+// epilogue runs under the other's main loop.
+template <int BN, int EPI> struct Cfg {
     static constexpr int kBTileBytes = BN * BK * 4;
     static constexpr int kStageBytes = kATileBytes + kBTileBytes;
-    static constexpr int kStages = BN == 128 ? 6 : 8;
-    static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*alignment slack*/ + 256 /*barriers*/;
+    static constexpr int kStages = EPI == EPI_WGRAD ? 3 : 6;
+    static constexpr int kCtasPerSm = EPI == EPI_WGRAD ? 2 : 1;
+    static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*alignment slack*/ + 256 /*barriers*/ + 512 /*bias*/;
     static constexpr int kTmemCols = BN;             // fp32 accumulator: 128 lanes x BN columns
+    // epilogue staging per warp: {activation tile (DGRAD), output tile, transposed output tile} x 16 KB
+    static constexpr int kWarpStage = EPI == EPI_WGRAD ? 16384 : 49152;
+    static constexpr int kOutOffset = EPI == EPI_WGRAD ? 0 : 16384;
+    static_assert(4 * kWarpStage <= kStages * kStageBytes, "epilogue staging must fit in the pipeline stages");
 };
-
-enum { EPI_FWD = 0, EPI_DGRAD = 1, EPI_WGRAD = 2 };
 
 #ifdef DDPB_GEMM_TIMELINE
 // Development aid (tools/gemm_timeline.py): clock64 stamps of CTA (0,0)'s producer and MMA threads.
 __device__ long long g_gemm_stamps[3][512];
 #define GEMM_STAMP(row, i) do { if (blockIdx.x == 0 && blockIdx.y == 0 && (i) < 512) g_gemm_stamps[row][i] = clock64(); } while (0)
+// Per-CTA wall-clock phases (globaltimer, ns): 0 entry, 1 set-up done, 2 accumulator ready, 3 epilogue done, 4 exit.
+__device__ long long g_gemm_phase[1024][8];
+__device__ __forceinline__ long long gtimer() { long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+#define GEMM_PHASE(i) do { const int cta_ = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x; if (cta_ < 1024) g_gemm_phase[cta_][i] = gtimer(); } while (0)
 #else
 #define GEMM_STAMP(row, i) do { } while (0)
+#define GEMM_PHASE(i) do { } while (0)
 #endif
 
+// The output tile, its transposed copy and (DGRAD) the activation tile travel by TMA; what is left here
+// is what the epilogue threads touch directly.
 struct EpiParams {
     const float *bias;        // FWD: [N]
-    const float *act_prev;    // DGRAD: [M, ld_out] activation whose sign is the LeakyReLU mask
-    float *out;               // FWD: act_out [M, ld_out]; DGRAD: dZ_prev [M, ld_out]; WGRAD: dW [M, ld_out]
-    float *out_t;             // FWD / DGRAD: transposed copy [N, ld_t]; WGRAD: bias gradient [M]
-    int ld_out, ld_t;
+    float *bias_grad;         // WGRAD: [M], column n_real of the product
+    int has_t;                // FWD / DGRAD: also store the transposed copy
     int apply_act;            // FWD: LeakyReLU after the bias
-    int n_real;               // WGRAD: Hin (column n_real of the product is the bias gradient)
+    int n_real;               // width of the stored tile (FWD / DGRAD: N; WGRAD: Hin, column Hin is the bias gradient)
 };
 
 // ---- PTX wrappers ---------------------------------------------------------------------------
@@ -99,6 +111,10 @@ __device__ __forceinline__ void tma_load_2d(unsigned dst, const CUtensorMap *map
     asm volatile(
         "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
         ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap *map, unsigned src, int c0, int c1) {
+    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+                 ::"l"(map), "r"(src), "r"(c0), "r"(c1) : "memory");
 }
 __device__ __forceinline__ unsigned cluster_ctarank() {
     unsigned r;
@@ -182,16 +198,22 @@ __device__ __forceinline__ unsigned make_idesc(bool b_mn_major) {
 }
 
 template <int EPI, bool B_MN, int BN, int SPLIT>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kThreads, Cfg<BN, EPI>::kCtasPerSm)
 gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                 const __grid_constant__ CUtensorMap map_o /* out, boxes [32 m][32 n], 128B swizzle */,
+                 const __grid_constant__ CUtensorMap map_t /* transposed out, boxes [32 n][32 m], no swizzle */,
+                 const __grid_constant__ CUtensorMap map_c /* DGRAD: act_prev, same geometry as map_o */,
                  const EpiParams ep, int M, int N, int K) {
-    constexpr int kStages = Cfg<BN>::kStages, kStageBytes = Cfg<BN>::kStageBytes, kTmemCols = Cfg<BN>::kTmemCols;
+    using C = Cfg<BN, EPI>;
+    constexpr int kStages = C::kStages, kStageBytes = C::kStageBytes, kTmemCols = C::kTmemCols;
     extern __shared__ unsigned char smem_raw[];
     // 1024-byte alignment for the swizzle atoms
     unsigned char *smem = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     unsigned long long *bars = reinterpret_cast<unsigned long long *>(smem + kStages * kStageBytes);
-    // bars[0..S) full, bars[S..2S) empty, bars[2S] accumulator ready, then the TMEM address slot
-    unsigned *tmem_slot = reinterpret_cast<unsigned *>(bars + 2 * kStages + 1);
+    // bars[0..S) full, bars[S..2S) empty, bars[2S] accumulator ready, bars[2S+1..2S+5) activation tile of
+    // epilogue warp q landed (DGRAD), then the TMEM address slot; the bias slice follows the barrier block
+    unsigned *tmem_slot = reinterpret_cast<unsigned *>(bars + 2 * kStages + 5);
+    float *bias_s = reinterpret_cast<float *>(smem + kStages * kStageBytes + 256);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n0 = blockIdx.x * BN, m0 = blockIdx.y * BM;
@@ -201,20 +223,28 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     const unsigned krank = SPLIT > 1 ? cluster_ctarank() : 0u;
     const int kb_begin = (int)((long long)num_k * krank / SPLIT), kb_count = (int)((long long)num_k * (krank + 1) / SPLIT) - kb_begin;
     if (threadIdx.x == 0) {
+        GEMM_PHASE(0);
         for (int s = 0; s < kStages; ++s) {
             mbar_init(saddr(&bars[s]), 1);
             mbar_init(saddr(&bars[kStages + s]), 1);
         }
-        mbar_init(saddr(&bars[2 * kStages]), 1);
+        for (int s = 0; s < 5; ++s) mbar_init(saddr(&bars[2 * kStages + s]), 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_o) : "memory");
+        if (EPI != EPI_WGRAD) asm volatile("prefetch.tensormap [%0];" ::"l"(&map_t) : "memory");
+        if (EPI == EPI_DGRAD) asm volatile("prefetch.tensormap [%0];" ::"l"(&map_c) : "memory");
     }
     if (warp == 2) tmem_alloc(saddr(tmem_slot), kTmemCols);
+    // The bias slice of this tile is fetched while the pipeline runs (a cold miss here costs ~1.5 us
+    // per 128-byte line when it sits in the epilogue instead).
+    if (EPI == EPI_FWD && warp >= 4) bias_s[threadIdx.x - 128] = (n0 + (int)threadIdx.x - 128 < N) ? __ldg(ep.bias + n0 + threadIdx.x - 128) : 0.f;
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const unsigned tmem_base = *tmem_slot;
+    if (threadIdx.x == 0) GEMM_PHASE(1);
 
     if (warp == 0) {
         // ===== TMA producer =====
@@ -265,6 +295,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     if (warp >= 4) {
         mbar_wait(saddr(&bars[2 * kStages]), 0);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        if (threadIdx.x == 128) GEMM_PHASE(2);
         if (SPLIT > 1 && krank > 0) {
             const int q = warp - 4;
 #pragma unroll 1
@@ -276,14 +307,28 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
             }
         }
     }
+    // Rank 0's own pipeline stages become the staging area of its epilogue: per epilogue warp
+    // {activation tile (DGRAD), output tile, transposed output tile}, each 4 chunks of [32][32] floats
+    // (WGRAD: the output tile only).
+    unsigned char *wstage = smem + (warp >= 4 ? warp - 4 : 0) * C::kWarpStage;
+    if (EPI == EPI_DGRAD && warp >= 4 && krank == 0 && lane == 0) {
+        // LeakyReLU mask source: rows [m0+32q, +32) x columns [n0, +128) of act_prev, fetched by TMA as
+        // soon as the stages are free (out-of-range parts arrive as zeros and are clipped on the store)
+        const unsigned bar = saddr(&bars[2 * kStages + 1 + (warp - 4)]);
+        mbar_expect_tx(bar, 16384);
+#pragma unroll
+        for (int c = 0; c < 4; ++c) tma_load_2d(saddr(wstage) + c * 4096, &map_c, bar, n0 + c * 32, m0 + (warp - 4) * 32);
+    }
     if (SPLIT > 1) {
         __syncthreads();
         cluster_sync_all();                                                          // partial tiles are parked
     }
     if (warp >= 4 && krank == 0) {
-        // ===== epilogue: TMEM (+ the other ranks' partials) -> registers -> global =====
+        // ===== epilogue: TMEM (+ the other ranks' partials) -> registers -> shared -> TMA store =====
         const int q = warp - 4;                                                      // TMEM lanes [32q, 32q+32)
         const int m = m0 + q * 32 + lane;
+        const int sw = lane & 7;                                                     // 128B swizzle: 16-byte chunk j of row r sits at j ^ (r & 7)
+        if (EPI == EPI_DGRAD) mbar_wait(saddr(&bars[2 * kStages + 1 + q]), 0);
 #pragma unroll 1
         for (int c0 = 0; c0 < BN; c0 += 32) {
             float v[32];
@@ -294,54 +339,56 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
 #pragma unroll
                     for (int i = 0; i < 32; ++i) v[i] += ld_dsmem_f32(park + (c0 + i) * BM + q * 32 + lane, r);
             }
-            const int nb = n0 + c0;
+            const int nb = n0 + c0, chunk = c0 >> 5;
             if (EPI == EPI_FWD) {
+                const float4 *bp = reinterpret_cast<const float4 *>(bias_s + c0);
 #pragma unroll
-                for (int i = 0; i < 32; ++i) {
-                    float z = v[i] + ((nb + i < N) ? __ldg(ep.bias + nb + i) : 0.f);
-                    v[i] = ep.apply_act ? (z > 0.f ? z : z * kSlope) : z;
+                for (int i = 0; i < 8; ++i) {
+                    const float4 b = bp[i];
+                    const float z0 = v[4 * i] + b.x, z1 = v[4 * i + 1] + b.y, z2 = v[4 * i + 2] + b.z, z3 = v[4 * i + 3] + b.w;
+                    v[4 * i + 0] = (ep.apply_act && z0 <= 0.f) ? z0 * kSlope : z0;
+                    v[4 * i + 1] = (ep.apply_act && z1 <= 0.f) ? z1 * kSlope : z1;
+                    v[4 * i + 2] = (ep.apply_act && z2 <= 0.f) ? z2 * kSlope : z2;
+                    v[4 * i + 3] = (ep.apply_act && z3 <= 0.f) ? z3 * kSlope : z3;
                 }
             } else if (EPI == EPI_DGRAD) {
-                if (m < M) {
-                    const float4 *ap = reinterpret_cast<const float4 *>(ep.act_prev + (size_t)m * ep.ld_out + nb);
+                const unsigned char *ap = wstage + chunk * 4096 + lane * 128;
 #pragma unroll
-                    for (int i = 0; i < 8; ++i) {
-                        const float4 a = (nb + 4 * i < N) ? __ldg(ap + i) : make_float4(1.f, 1.f, 1.f, 1.f);
-                        v[4 * i + 0] = a.x > 0.f ? v[4 * i + 0] : v[4 * i + 0] * kSlope;
-                        v[4 * i + 1] = a.y > 0.f ? v[4 * i + 1] : v[4 * i + 1] * kSlope;
-                        v[4 * i + 2] = a.z > 0.f ? v[4 * i + 2] : v[4 * i + 2] * kSlope;
-                        v[4 * i + 3] = a.w > 0.f ? v[4 * i + 3] : v[4 * i + 3] * kSlope;
-                    }
+                for (int i = 0; i < 8; ++i) {
+                    const float4 a = *reinterpret_cast<const float4 *>(ap + ((i ^ sw) << 4));
+                    v[4 * i + 0] = a.x > 0.f ? v[4 * i + 0] : v[4 * i + 0] * kSlope;
+                    v[4 * i + 1] = a.y > 0.f ? v[4 * i + 1] : v[4 * i + 1] * kSlope;
+                    v[4 * i + 2] = a.z > 0.f ? v[4 * i + 2] : v[4 * i + 2] * kSlope;
+                    v[4 * i + 3] = a.w > 0.f ? v[4 * i + 3] : v[4 * i + 3] * kSlope;
                 }
             }
-            if (EPI == EPI_WGRAD) {
-                if (m < M) {
-                    if (nb < ep.n_real) {                                            // dW rows, 128 B per thread and chunk
-                        float4 *op = reinterpret_cast<float4 *>(ep.out + (size_t)m * ep.ld_out + nb);
+            unsigned char *so = wstage + C::kOutOffset + chunk * 4096;               // [32 m][32 n], swizzled
+            float *st = reinterpret_cast<float *>(wstage + 32768 + chunk * 4096);    // [32 n][32 m]
+            const bool store_o = nb < ep.n_real, store_t = EPI != EPI_WGRAD && ep.has_t && nb < N;
+            if (store_o) {
 #pragma unroll
-                        for (int i = 0; i < 8; ++i)
-                            if (nb + 4 * i < ep.n_real) op[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
-                    } else if (nb == ep.n_real) {
-                        ep.out_t[m] = v[0];                                          // product with the row of ones
-                    }
-                }
-            } else {
-                if (m < M) {
-                    float4 *op = reinterpret_cast<float4 *>(ep.out + (size_t)m * ep.ld_out + nb);
-#pragma unroll
-                    for (int i = 0; i < 8; ++i)
-                        if (nb + 4 * i < N) op[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
-                }
-                if (ep.out_t) {                                                      // transposed copy: lanes = consecutive m
-#pragma unroll
-                    for (int i = 0; i < 32; ++i)
-                        if (nb + i < N && m < M) ep.out_t[(size_t)(nb + i) * ep.ld_t + m] = v[i];
-                }
+                for (int i = 0; i < 8; ++i)
+                    *reinterpret_cast<float4 *>(so + lane * 128 + ((i ^ sw) << 4)) = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
             }
+            if (store_t) {
+#pragma unroll
+                for (int i = 0; i < 32; ++i) st[i * 32 + lane] = v[i];
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");              // generic-proxy writes -> visible to the TMA engine
+            __syncwarp();
+            if (lane == 0) {
+                if (store_o) tma_store_2d(&map_o, saddr(so), nb, m0 + q * 32);      // rows >= M and columns >= n_real are clipped
+                if (store_t) tma_store_2d(&map_t, saddr(st), m0 + q * 32, nb);
+                asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            }
+            if (EPI == EPI_WGRAD && nb == ep.n_real && m < M) ep.bias_grad[m] = v[0];   // product with the row of ones
         }
+        if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // staging must outlive the bulk reads
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        if (threadIdx.x == 128) GEMM_PHASE(3);
     }
     __syncthreads();
+    if (threadIdx.x == 0) GEMM_PHASE(4);
     if (SPLIT > 1) cluster_sync_all();                 // nobody leaves while rank 0 may still read its parked tile
     if (warp == 2) {
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -383,25 +430,29 @@ int make_map(CUtensorMap *map, const float *base, long long rows, long long cols
     return 0;
 }
 
+// The five tensor maps of one launch: operands A and B, the output tile, its transposed copy and
+// (DGRAD) the activation whose sign is the LeakyReLU mask.  Unused ones repeat the output map.
+struct Maps { CUtensorMap a, b, o, t, c; };
+
 template <int EPI, bool B_MN, int BN, int SPLIT>
-int launch(const CUtensorMap &ma, const CUtensorMap &mb, const EpiParams &ep, int M, int N, int K, cudaStream_t stream) {
+int launch(const Maps &mp, const EpiParams &ep, int M, int N, int K, cudaStream_t stream) {
     static bool configured = false;
     if (!configured) {
         DDPB_CUDA(cudaFuncSetAttribute(gemm_tf32_kernel<EPI, B_MN, BN, SPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       Cfg<BN>::kSmemBytes));
+                                       Cfg<BN, EPI>::kSmemBytes));
         configured = true;
     }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((N + BN - 1) / BN, (M + BM - 1) / BM, SPLIT);
     cfg.blockDim = dim3(kThreads);
-    cfg.dynamicSmemBytes = Cfg<BN>::kSmemBytes;
+    cfg.dynamicSmemBytes = Cfg<BN, EPI>::kSmemBytes;
     cfg.stream = stream;
     cudaLaunchAttribute attr;
     attr.id = cudaLaunchAttributeClusterDimension;
     attr.val.clusterDim.x = 1; attr.val.clusterDim.y = 1; attr.val.clusterDim.z = SPLIT;
     cfg.attrs = &attr;
     cfg.numAttrs = 1;
-    DDPB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tf32_kernel<EPI, B_MN, BN, SPLIT>, ma, mb, ep, M, N, K));
+    DDPB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tf32_kernel<EPI, B_MN, BN, SPLIT>, mp.a, mp.b, mp.o, mp.t, mp.c, ep, M, N, K));
     return 0;
 }
 
@@ -413,18 +464,18 @@ int split_for(int M, int N, int K) {
         forced = e ? atoi(e) : 0;
     }
     const long long tiles = (long long)((M + BM - 1) / BM) * ((N + 127) / 128);
-    int s = forced ? forced : (tiles >= 100 ? 1 : tiles >= 50 ? 2 : 4);
+    int s = forced ? forced : (tiles >= 100 ? 1 : 2);          // measured: 4-way never beats 2-way (H = 1024, 4096)
     if (s != 1 && s != 2 && s != 4) s = 1;
     while (s > 1 && (K + BK - 1) / BK < 4 * s) s >>= 1;       // keep a few k-blocks per rank
     return s;
 }
 
 template <int EPI, bool B_MN>
-int launch_split(const CUtensorMap &ma, const CUtensorMap &mb, const EpiParams &ep, int M, int N, int K, cudaStream_t stream) {
+int launch_split(const Maps &mp, const EpiParams &ep, int M, int N, int K, cudaStream_t stream) {
     switch (split_for(M, N, K)) {
-        case 4: return launch<EPI, B_MN, 128, 4>(ma, mb, ep, M, N, K, stream);
-        case 2: return launch<EPI, B_MN, 128, 2>(ma, mb, ep, M, N, K, stream);
-        default: return launch<EPI, B_MN, 128, 1>(ma, mb, ep, M, N, K, stream);
+        case 4: return launch<EPI, B_MN, 128, 4>(mp, ep, M, N, K, stream);
+        case 2: return launch<EPI, B_MN, 128, 2>(mp, ep, M, N, K, stream);
+        default: return launch<EPI, B_MN, 128, 1>(mp, ep, M, N, K, stream);
     }
 }
 
@@ -435,6 +486,10 @@ DDPB_API int ddpb_gemm_stamps(long long *host_out /* [3*512] */) {
     DDPB_CUDA(cudaMemcpyFromSymbol(host_out, g_gemm_stamps, sizeof(long long) * 3 * 512));
     return 0;
 }
+DDPB_API int ddpb_gemm_phases(long long *host_out /* [1024*8] */) {
+    DDPB_CUDA(cudaMemcpyFromSymbol(host_out, g_gemm_phase, sizeof(long long) * 1024 * 8));
+    return 0;
+}
 #endif
 
 DDPB_API int ddpb_linear_fwd(const float *act_in, const float *W, const float *bias, float *act_out, float *act_out_t,
@@ -442,11 +497,16 @@ DDPB_API int ddpb_linear_fwd(const float *act_in, const float *W, const float *b
     DDPB_REQUIRE(act_in && W && bias && act_out && B >= 1 && Hin >= 32 && Hout >= 32 && Hin % 4 == 0 && Hout % 4 == 0,
                  "ddpb_linear_fwd: bad arguments (B=%d Hin=%d Hout=%d)", B, Hin, Hout);
     DDPB_REQUIRE(!act_out_t || ld_t >= B, "ddpb_linear_fwd: transposed pitch %d < batch %d", ld_t, B);
-    CUtensorMap ma, mb;
-    if (int rc = make_map(&ma, act_in, B, Hin, Hin, BM, BK)) return rc;
-    if (int rc = make_map(&mb, W, Hout, Hin, Hin, 128, BK)) return rc;
-    EpiParams ep = {bias, nullptr, act_out, act_out_t, Hout, ld_t, apply_act, 0};
-    return launch_split<EPI_FWD, false>(ma, mb, ep, B, Hout, Hin, (cudaStream_t)stream);
+    DDPB_REQUIRE(!act_out_t || ld_t % 4 == 0, "ddpb_linear_fwd: transposed pitch %d must be a multiple of 4", ld_t);
+    Maps mp;
+    if (int rc = make_map(&mp.a, act_in, B, Hin, Hin, BM, BK)) return rc;
+    if (int rc = make_map(&mp.b, W, Hout, Hin, Hin, 128, BK)) return rc;
+    if (int rc = make_map(&mp.o, act_out, B, Hout, Hout, 32, 32)) return rc;
+    mp.t = mp.c = mp.o;
+    if (act_out_t)
+        if (int rc = make_map(&mp.t, act_out_t, Hout, B, ld_t, 32, 32, CU_TENSOR_MAP_SWIZZLE_NONE)) return rc;
+    EpiParams ep = {bias, nullptr, act_out_t != nullptr, apply_act, Hout};
+    return launch_split<EPI_FWD, false>(mp, ep, B, Hout, Hin, (cudaStream_t)stream);
 }
 
 DDPB_API int ddpb_linear_dgrad(const float *dz, const float *W, const float *act_prev, float *dz_prev, float *dz_prev_t,
@@ -454,20 +514,28 @@ DDPB_API int ddpb_linear_dgrad(const float *dz, const float *W, const float *act
     DDPB_REQUIRE(dz && W && act_prev && dz_prev && B >= 1 && Hin >= 32 && Hout >= 32 && Hin % 4 == 0 && Hout % 4 == 0,
                  "ddpb_linear_dgrad: bad arguments (B=%d Hin=%d Hout=%d)", B, Hin, Hout);
     DDPB_REQUIRE(!dz_prev_t || ld_t >= B, "ddpb_linear_dgrad: transposed pitch %d < batch %d", ld_t, B);
-    CUtensorMap ma, mb;
-    if (int rc = make_map(&ma, dz, B, Hout, Hout, BM, BK)) return rc;                 // A: [m = sample][k = out neuron]
-    if (int rc = make_map(&mb, W, Hout, Hin, Hin, BK, 32, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B)) return rc;   // B: boxes [32 k][32 n], n contiguous
-    EpiParams ep = {nullptr, act_prev, dz_prev, dz_prev_t, Hin, ld_t, 0, 0};
-    return launch_split<EPI_DGRAD, true>(ma, mb, ep, B, Hin, Hout, (cudaStream_t)stream);
+    DDPB_REQUIRE(!dz_prev_t || ld_t % 4 == 0, "ddpb_linear_dgrad: transposed pitch %d must be a multiple of 4", ld_t);
+    Maps mp;
+    if (int rc = make_map(&mp.a, dz, B, Hout, Hout, BM, BK)) return rc;               // A: [m = sample][k = out neuron]
+    if (int rc = make_map(&mp.b, W, Hout, Hin, Hin, BK, 32, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B)) return rc;   // B: boxes [32 k][32 n], n contiguous
+    if (int rc = make_map(&mp.o, dz_prev, B, Hin, Hin, 32, 32)) return rc;
+    if (int rc = make_map(&mp.c, act_prev, B, Hin, Hin, 32, 32)) return rc;
+    mp.t = mp.o;
+    if (dz_prev_t)
+        if (int rc = make_map(&mp.t, dz_prev_t, Hin, B, ld_t, 32, 32, CU_TENSOR_MAP_SWIZZLE_NONE)) return rc;
+    EpiParams ep = {nullptr, nullptr, dz_prev_t != nullptr, 0, Hin};
+    return launch_split<EPI_DGRAD, true>(mp, ep, B, Hin, Hout, (cudaStream_t)stream);
 }
 
 DDPB_API int ddpb_linear_wgrad(const float *dz_t, const float *act_t_ext, float *dW, float *db, int B, int Hin, int Hout,
                                int ld_t, void *stream) {
     DDPB_REQUIRE(dz_t && act_t_ext && dW && db && B >= 1 && Hin >= 32 && Hout >= 32 && Hin % 4 == 0 && ld_t % 4 == 0 && ld_t >= B,
                  "ddpb_linear_wgrad: bad arguments (B=%d Hin=%d Hout=%d ld_t=%d)", B, Hin, Hout, ld_t);
-    CUtensorMap ma, mb;
-    if (int rc = make_map(&ma, dz_t, Hout, B, ld_t, BM, BK)) return rc;               // A: [m = out neuron][k = sample]
-    if (int rc = make_map(&mb, act_t_ext, Hin + 1, B, ld_t, 128, BK)) return rc;      // B: [n = in neuron | ones][k = sample]
-    EpiParams ep = {nullptr, nullptr, dW, db, Hin, 0, 0, Hin};
-    return launch<EPI_WGRAD, false, 128, 1>(ma, mb, ep, Hout, Hin + 1, B, (cudaStream_t)stream);
+    Maps mp;
+    if (int rc = make_map(&mp.a, dz_t, Hout, B, ld_t, BM, BK)) return rc;             // A: [m = out neuron][k = sample]
+    if (int rc = make_map(&mp.b, act_t_ext, Hin + 1, B, ld_t, 128, BK)) return rc;    // B: [n = in neuron | ones][k = sample]
+    if (int rc = make_map(&mp.o, dW, Hout, Hin, Hin, 32, 32)) return rc;              // dW rows straight into the flat gradient bucket
+    mp.t = mp.c = mp.o;
+    EpiParams ep = {nullptr, db, 0, 0, Hin};
+    return launch<EPI_WGRAD, false, 128, 1>(mp, ep, Hout, Hin + 1, B, (cudaStream_t)stream);
 }
