@@ -149,7 +149,7 @@ def reference_arm(args):
                                        f"(host has {cores} cores), stock torch CPU path (oracle/torch_ref.py, "
                                        "bit-identical to the reference run)"},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # --------------------------------------------------------------------------------------
@@ -387,12 +387,30 @@ def ours(args):
                              "note": "latency-bound by construction: 2 clusters x 8 CTAs, 273 KB and 1 MFLOP per launch"},
                 "cpu_baseline": cpu_baseline,
                 "loss_after_bench": [float(v) for v in last] if last else None}
-        print(json.dumps(line), flush=True)
+        emit(line)
     eng.destroy_comm()
     dist.destroy_process_group()
 
 
+_RESULT_FD = None
+
+
+def emit(line):
+    """The one JSON line, written to the process's original stdout."""
+    data = (json.dumps(line) + "\n").encode()
+    if _RESULT_FD is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_RESULT_FD, data)
+
+
 def main():
+    # Libraries write to stdout too (NCCL prints its version banner there when NCCL_DEBUG is set on
+    # the box): keep fd 1 for the result line only and send everything else to stderr.
+    global _RESULT_FD
+    sys.stdout.flush()
+    _RESULT_FD = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=int(os.environ.get("WORLD_SIZE", "1")))
     ap.add_argument("--steps", type=int, default=2000)

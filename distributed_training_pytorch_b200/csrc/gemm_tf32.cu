@@ -5,7 +5,7 @@
 // Reference: the same nn.Linear layers (toy_model_and_data.py:13-21, widths scaled up) that
 // PyTorch runs as cuBLAS sgemm calls in forward and in autograd's backward (demo.py:104-109).
 //
-//   D[m][n] = sum_k A(m,k) * B(n,k)          one 128 x BN output tile per CTA (BN = 128 or 64)
+//   D[m][n] = sum_k A(m,k) * B(n,k)          one 128 x 128 output tile per CTA (or per cluster, see below)
 //
 //   forward   m = sample, n = output neuron, k = input neuron   A = act_in [B,Hin]   K-major
 //                                                                B = W [Hout,Hin]      K-major
@@ -18,23 +18,33 @@
 //             epilogue: store dW straight into the flat gradient bucket; the operand row
 //             n = Hin is a row of ones, which makes column Hin of the product the bias gradient
 //
-// Measured (tools/gemm_timeline.py, clock64 stamps in the MMA thread): a CTA retires one 32-wide
-// k-block every ~490 cycles = four 128x128x8 tf32 MMAs at ~123 cycles each, i.e. the tensor pipe of
-// an SM that has a tile is saturated (1024 tf32 MAC/clk/SM); data always lands ~3500 cycles after it
-// was requested and the 6-stage ring hides that.  Tiles larger, multicast of the shared A slab and
-// L2 prefetch of the weight tiles were all tried and change nothing, because the bound is not
-// memory.  What was wrong at B <= 256 was the NUMBER of tiles: 2 x H/128 (64 at H = 4096) for 148
-// SMs.  So the K loop is split across a cluster of SPLIT CTAs (blockIdx.z): ranks > 0 park their
-// partial accumulator in their own shared memory, rank 0 adds them through distributed shared
-// memory in its epilogue.
+// Measured (tools/gemm_timeline.py: clock64 stamps in the producer and MMA threads, globaltimer
+// stamps per CTA and phase):
+//   * main loop: a CTA retires one 32-wide k-block (16 KB of A + 16 KB of B) every ~0.31 us when 64
+//     CTAs run and ~0.38 us when 128 run; a k-block is requested ~2600 cycles before it lands and the
+//     6-stage ring hides that.  Multicast of the shared A slab, 2x2 clusters of neighbouring tiles, L2
+//     prefetch of the weight tiles and 64-wide tiles were all tried: no gain.  Every operand byte
+//     crosses shared memory twice (TMA write, tensor-core read) and every weight tile is fetched by
+//     both batch halves, so L2 -> SM traffic is 4x the weight bytes.
+//   * too few tiles at B <= 256: 2 x H/128 (64 at H = 4096) for 148 SMs.  So the K loop is split
+//     across a cluster of SPLIT CTAs (blockIdx.z): ranks > 0 park their partial accumulator in their
+//     own shared memory, rank 0 adds them through distributed shared memory in its epilogue (2-way:
+//     49 -> 38 us at H = 4096; 4-way never wins, its 256 CTAs need two waves).
+//   * epilogue: the first version stored straight from registers (each lane its own row: 32 rows x
+//     16 B per instruction) and read the bias / activation rows the same way -- 11 us per launch, each
+//     128-byte line a serialised cold miss of ~1.5 us.  Now the bias slice is fetched during the main
+//     loop, the activation tile (dgrad) arrives by TMA, and the output tile and its transpose go
+//     through shared memory (the dead pipeline stages) and leave as TMA bulk stores: 2.8 us.
+//   * wgrad (K = B, thousands of tiles): 3-stage ring and two CTAs per SM, so one CTA's epilogue runs
+//     under the other's main loop (54 -> 35 us at H = 4096).
 // Structure (one CTA, 256 threads): warp 0 = TMA producer, warp 1 = MMA issuer (one elected
 // thread), warp 2 = TMEM allocator, warps 4..7 = epilogue (tcgen05.ld 32 lanes x 32 columns at a
 // time).  A 6-stage ring of {A tile, B tile} (32 KB per stage, 128-byte swizzle) is filled by
 // cp.async.bulk.tensor with mbarrier complete_tx and drained by tcgen05.commit.
 // Operands are fp32 in HBM and shared memory; the tensor core reads them as tf32 (10-bit
 // mantissa) and accumulates in fp32 in TMEM -- the tolerance of this path is stated in
-// tests/test_gpu_wide.py.  These GEMMs sit at the HBM/tensor ridge for B <= 256 (each weight byte
-// feeds 128 FLOP per pass): the roofline is weight bytes / HBM bandwidth.
+// tests/test_gpu_wide.py.  At B <= 256 each weight byte feeds 128 FLOP per pass, below the tf32 ridge
+// (~170 FLOP/B): the roofline is weight bytes / HBM bandwidth.
 #include "common.cuh"
 #include <cuda.h>
 #include <cstdlib>
@@ -125,13 +135,32 @@ __device__ __forceinline__ void cluster_sync_all() {
     asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
     asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
-__device__ __forceinline__ float ld_dsmem_f32(const float *local, unsigned rank) {
+// v[0..32) += the 128 contiguous bytes at `local` in the shared memory of cluster rank `rank`.  One asm
+// block, so that the eight 16-byte loads are in flight together (issued one by one, each waiting for
+// the previous, this reduction cost ~9 us per tile).
+__device__ __forceinline__ void add_dsmem_row(const void *local, unsigned rank, float (&v)[32]) {
     unsigned remote;
-    float v;
+    float r[32];
     asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(saddr(local)), "r"(rank));
-    asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(remote) : "memory");
-    return v;
+    asm volatile(
+        "ld.shared::cluster.v4.f32 {%0, %1, %2, %3}, [%32];\n\t"
+        "ld.shared::cluster.v4.f32 {%4, %5, %6, %7}, [%32+16];\n\t"
+        "ld.shared::cluster.v4.f32 {%8, %9, %10, %11}, [%32+32];\n\t"
+        "ld.shared::cluster.v4.f32 {%12, %13, %14, %15}, [%32+48];\n\t"
+        "ld.shared::cluster.v4.f32 {%16, %17, %18, %19}, [%32+64];\n\t"
+        "ld.shared::cluster.v4.f32 {%20, %21, %22, %23}, [%32+80];\n\t"
+        "ld.shared::cluster.v4.f32 {%24, %25, %26, %27}, [%32+96];\n\t"
+        "ld.shared::cluster.v4.f32 {%28, %29, %30, %31}, [%32+112];"
+        : "=f"(r[0]), "=f"(r[1]), "=f"(r[2]), "=f"(r[3]), "=f"(r[4]), "=f"(r[5]), "=f"(r[6]), "=f"(r[7]),
+          "=f"(r[8]), "=f"(r[9]), "=f"(r[10]), "=f"(r[11]), "=f"(r[12]), "=f"(r[13]), "=f"(r[14]), "=f"(r[15]),
+          "=f"(r[16]), "=f"(r[17]), "=f"(r[18]), "=f"(r[19]), "=f"(r[20]), "=f"(r[21]), "=f"(r[22]), "=f"(r[23]),
+          "=f"(r[24]), "=f"(r[25]), "=f"(r[26]), "=f"(r[27]), "=f"(r[28]), "=f"(r[29]), "=f"(r[30]), "=f"(r[31])
+        : "r"(remote) : "memory");
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] += r[i];
 }
+constexpr int kParkRow = 144;                        // bytes per parked row of 32 floats: 128 + 16 of padding (conflict-free v4)
+constexpr int kParkChunk = BM * kParkRow;            // one 32-column chunk of the partial tile
 __device__ __forceinline__ void tmem_alloc(unsigned slot_smem, unsigned cols) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(slot_smem), "r"(cols) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
@@ -290,8 +319,8 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         }
     }
     // The pipeline stages are dead once the accumulator is complete: with SPLIT > 1 they become the
-    // parking area of the partial tile, laid out [column][row] so that lanes (rows) are contiguous.
-    float *park = reinterpret_cast<float *>(smem);
+    // parking area of the partial tile: [chunk of 32 columns][row][32 floats + pad].
+    unsigned char *park = smem;
     if (warp >= 4) {
         mbar_wait(saddr(&bars[2 * kStages]), 0);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -302,8 +331,9 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
             for (int c0 = 0; c0 < BN; c0 += 32) {
                 float v[32];
                 tmem_ld32(tmem_base + ((unsigned)(q * 32) << 16) + (unsigned)c0, v);
+                float4 *pr = reinterpret_cast<float4 *>(park + (c0 >> 5) * kParkChunk + (q * 32 + lane) * kParkRow);
 #pragma unroll
-                for (int i = 0; i < 32; ++i) park[(c0 + i) * BM + q * 32 + lane] = v[i];
+                for (int i = 0; i < 8; ++i) pr[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
             }
         }
     }
@@ -336,8 +366,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
             if (SPLIT > 1) {
 #pragma unroll 1
                 for (unsigned r = 1; r < (unsigned)SPLIT; ++r)
-#pragma unroll
-                    for (int i = 0; i < 32; ++i) v[i] += ld_dsmem_f32(park + (c0 + i) * BM + q * 32 + lane, r);
+                    add_dsmem_row(park + (c0 >> 5) * kParkChunk + (q * 32 + lane) * kParkRow, r, v);
             }
             const int nb = n0 + c0, chunk = c0 >> 5;
             if (EPI == EPI_FWD) {
