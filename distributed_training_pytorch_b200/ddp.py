@@ -63,7 +63,7 @@ class Output:
 
 class DistributedDataParallel:
     def __init__(self, module, device_ids=None, output_device=None, dim=0, broadcast_buffers=True,
-                 process_group=None, bucket_cap_mb=25, find_unused_parameters=False,
+                 process_group=None, bucket_cap_mb=None, find_unused_parameters=False,
                  gradient_as_bucket_view=True, static_graph=False, lazy_step=None, **unused):
         self.module = module
         self.process_group = process_group
