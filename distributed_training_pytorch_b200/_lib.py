@@ -17,6 +17,8 @@ MAX_JOBS = 4
 MAX_PEERS = 8
 XCHG_ROW = 376
 XCHG_WINDOW_BYTES = 2 * MAX_PEERS * XCHG_ROW * 8
+BUCKET_MAX = 1024
+BUCKET_FLAGS_BYTES = 2 * BUCKET_MAX * MAX_PEERS * 4 + BUCKET_MAX * 4
 TOY_HIDDEN, TOY_PARAMS = 10, 371
 
 
@@ -49,6 +51,15 @@ class SegJob(ctypes.Structure):
                 ("lr", c_double), ("beta1", c_double), ("beta2", c_double), ("eps", c_double), ("momentum", c_double)]
 
 
+class BucketJob(ctypes.Structure):          # ddpb_bucket_job
+    _fields_ = [("window", c_void_p * MAX_PEERS), ("grads_off", c_int64), ("params_off", c_int64),
+                ("m", c_void_p), ("v", c_void_p), ("bias_table", c_void_p), ("state", c_void_p),
+                ("start", c_int64), ("n", c_int64), ("ticket", c_int64),
+                ("bias_table_n", c_int32), ("world", c_int32), ("rank", c_int32), ("bucket_index", c_int32),
+                ("mode", c_int32), ("advance", c_int32),
+                ("beta1", c_double), ("beta2", c_double), ("eps", c_double), ("grad_scale", c_float), ("reserved", c_int32)]
+
+
 _SIGNATURES = {
     "ddpb_version": (c_int, []),
     "ddpb_last_error": (c_char_p, []),
@@ -76,6 +87,7 @@ _SIGNATURES = {
     "ddpb_fused_avg_adam_dev": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_float,
                                         c_double, c_double, c_double, c_void_p, c_int, c_void_p, c_int, c_void_p]),
     "ddpb_fused_avg_sgd": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_float, c_double, c_double, c_int64, c_void_p]),
+    "ddpb_bucket_reduce_adam": (c_int, [c_void_p, c_void_p]),
     "ddpb_nccl_load": (c_int, [c_char_p]),
     "ddpb_get_unique_id": (c_int, [c_void_p]),
     "ddpb_comm_create": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p]),

@@ -107,6 +107,168 @@ avg_sgd_kernel(const float *__restrict__ bucket, float *__restrict__ p, float *_
     }
 }
 
+// ---- bucket all-reduce fused with Adam over peer windows (ddpb_bucket_reduce_adam) -----------
+__device__ __forceinline__ float4 ld_sys_f4(const float4 *p) {
+    float4 v;
+    asm volatile("ld.relaxed.sys.global.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_sys_f4(float4 *p, float4 v) {
+    asm volatile("st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ float ld_sys_f1(const float *p) {
+    float v;
+    asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_sys_f1(float *p, float v) {
+    asm volatile("st.relaxed.sys.global.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
+}
+__device__ __forceinline__ void st_release_sys_i32(int *p, int v) {
+    asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ int ld_acquire_sys_i32(const int *p) {
+    int v;
+    asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+// Spin until *flag >= ticket; after ~5 s record the failure in state->reserved[0] and give up.
+__device__ __forceinline__ void wait_flag(const int *flag, int ticket, ddpb_opt_state *state) {
+    const unsigned long long t0 = global_ns();
+    while (ld_acquire_sys_i32(flag) < ticket) {
+        if (global_ns() - t0 > 5000000000ull) {
+            state->reserved[0] = 1;
+            break;
+        }
+        __nanosleep(100);
+    }
+}
+
+// Flags of one window: ready[bucket][source rank], done[bucket][source rank], then a CTA counter
+// per bucket (used only by the window's owner).
+struct BucketFlags {
+    int ready[DDPB_BUCKET_MAX][DDPB_MAX_PEERS];
+    int done[DDPB_BUCKET_MAX][DDPB_MAX_PEERS];
+    unsigned counter[DDPB_BUCKET_MAX];
+};
+static_assert(sizeof(BucketFlags) == DDPB_BUCKET_FLAGS_BYTES, "flag block layout");
+
+template <int W>
+__global__ void __launch_bounds__(256)
+bucket_reduce_adam_kernel(const __grid_constant__ ddpb_bucket_job job) {
+    const int r = job.rank, b = job.bucket_index, t = (int)job.ticket;
+    BucketFlags *mine = reinterpret_cast<BucketFlags *>(job.window[r]);
+    __shared__ int s_last;
+
+    // 1. every rank has produced this bucket (and, having got that far, no longer reads the layer's
+    //    old parameters): tell the peers that we have, wait until they all have
+    if (job.mode) {
+#pragma unroll
+        for (int q = 0; q < W; ++q)
+            if ((int)threadIdx.x == q && q != r) {
+                if (blockIdx.x == 0) st_release_sys_i32(&reinterpret_cast<BucketFlags *>(job.window[q])->ready[b][r], t);
+                wait_flag(&mine->ready[b][q], t, job.state);
+            }
+        __syncthreads();
+    }
+
+    AdamScalars k;
+    {
+        const long long step = job.state->step;
+        const float2 bias = reinterpret_cast<const float2 *>(job.bias_table)[step < job.bias_table_n ? step : job.bias_table_n - 1];
+        k.w1 = (float)(1.0 - job.beta1); k.b2 = (float)job.beta2; k.w2 = (float)(1.0 - job.beta2);
+        k.bc2_sqrt = bias.y; k.eps = (float)job.eps; k.neg_step = bias.x; k.grad_scale = job.grad_scale;
+    }
+
+    // 2-4. this rank's shard, 16 bytes per thread and iteration
+    const long long n4 = job.n >> 2, per = (n4 + W - 1) / W;
+    const long long g0 = per * r, g1 = (g0 + per < n4) ? g0 + per : n4;
+    const long long first4 = job.start >> 2;
+    const float4 *grads[W];
+    float4 *params[W];
+#pragma unroll
+    for (int q = 0; q < W; ++q) {
+        grads[q] = reinterpret_cast<const float4 *>(reinterpret_cast<const char *>(job.window[q]) + job.grads_off) + first4;
+        params[q] = reinterpret_cast<float4 *>(reinterpret_cast<char *>(job.window[q]) + job.params_off) + first4;
+    }
+    const float4 *lg = reinterpret_cast<const float4 *>(reinterpret_cast<const char *>(mine) + job.grads_off) + first4;
+    float4 *lp = reinterpret_cast<float4 *>(reinterpret_cast<char *>(mine) + job.params_off) + first4;
+    float4 *m4 = reinterpret_cast<float4 *>(job.m) + first4, *v4 = reinterpret_cast<float4 *>(job.v) + first4;
+    const long long nthreads = (long long)gridDim.x * blockDim.x;
+    for (long long i = g0 + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < g1; i += nthreads) {
+        float4 part[W];
+        if (job.mode) {
+#pragma unroll
+            for (int q = 0; q < W; ++q)                      // all peers' loads in flight together; fixed order of the sum
+                part[q] = (q == r) ? __ldcs(grads[q] + i) : ld_sys_f4(grads[q] + i);
+        } else {
+            part[0] = __ldcs(lg + i);
+        }
+        float4 pp = lp[i], mm = m4[i], vv = v4[i];
+        float4 g = part[0];
+        if (job.mode) {
+#pragma unroll
+            for (int q = 1; q < W; ++q) {
+                g.x = __fadd_rn(g.x, part[q].x); g.y = __fadd_rn(g.y, part[q].y);
+                g.z = __fadd_rn(g.z, part[q].z); g.w = __fadd_rn(g.w, part[q].w);
+            }
+        }
+        adam_one(g.x, pp.x, mm.x, vv.x, k);
+        adam_one(g.y, pp.y, mm.y, vv.y, k);
+        adam_one(g.z, pp.z, mm.z, vv.z, k);
+        adam_one(g.w, pp.w, mm.w, vv.w, k);
+        m4[i] = mm; v4[i] = vv;
+#pragma unroll
+        for (int q = 0; q < W; ++q) {
+            if (q == r) params[q][i] = pp;
+            else st_sys_f4(params[q] + i, pp);
+        }
+    }
+    // the 1-3 elements after the last full group of four (only the last layer's bucket has them)
+    if (r == W - 1 && blockIdx.x == 0 && threadIdx.x < (job.n & 3)) {
+        const long long e = job.start + (n4 << 2) + threadIdx.x;
+        float g = 0.f;
+        for (int q = 0; q < W; ++q) {
+            if (!job.mode && q != r) continue;
+            const float *gq = reinterpret_cast<const float *>(reinterpret_cast<const char *>(job.window[q]) + job.grads_off);
+            g = __fadd_rn(g, q == r ? gq[e] : ld_sys_f1(gq + e));
+        }
+        float *pr = reinterpret_cast<float *>(reinterpret_cast<char *>(job.window[r]) + job.params_off);
+        float pp = pr[e], mm = job.m[e], vv = job.v[e];
+        adam_one(g, pp, mm, vv, k);
+        job.m[e] = mm; job.v[e] = vv;
+        for (int q = 0; q < W; ++q) {
+            float *pq = reinterpret_cast<float *>(reinterpret_cast<char *>(job.window[q]) + job.params_off);
+            if (q == r) pq[e] = pp; else st_sys_f1(pq + e, pp);
+        }
+    }
+
+    // the last CTA to finish tells the peers that our shard has been pushed everywhere and waits for
+    // theirs; the other CTAs leave (only one CTA per GPU ever spins here, so grids larger than the
+    // machine cannot deadlock against each other)
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        s_last = atomicAdd(&mine->counter[b], 1u) == gridDim.x - 1;
+        __threadfence();
+    }
+    __syncthreads();
+    if (s_last) {
+        if (threadIdx.x == 0) mine->counter[b] = 0;
+#pragma unroll
+        for (int q = 0; q < W; ++q)
+            if ((int)threadIdx.x == q && q != r) {
+                st_release_sys_i32(&reinterpret_cast<BucketFlags *>(job.window[q])->done[b][r], t);
+                wait_flag(&mine->done[b][q], t, job.state);
+            }
+    }
+}
+
 int stream_grid(long long n, int per_thread) {
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
@@ -151,5 +313,49 @@ DDPB_API int ddpb_fused_avg_sgd(const float *bucket, float *p, float *buf, int64
     avg_sgd_kernel<<<stream_grid(n, 1), 256, 0, (cudaStream_t)stream>>>(bucket, p, buf, n, grad_scale, (float)lr,
                                                                          (float)momentum, step == 1);
     DDPB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+namespace {
+template <int W>
+int launch_bucket(const ddpb_bucket_job &job, cudaStream_t stream) {
+    const long long n4 = job.n >> 2, per = (n4 + W - 1) / W;
+    bucket_reduce_adam_kernel<W><<<stream_grid(per * 4, 4), 256, 0, stream>>>(job);
+    DDPB_CUDA(cudaGetLastError());
+    return 0;
+}
+}  // namespace
+
+DDPB_API int ddpb_bucket_reduce_adam(const ddpb_bucket_job *job, void *stream) {
+    DDPB_REQUIRE(job && job->m && job->v && job->bias_table && job->state && job->bias_table_n >= 1,
+                 "ddpb_bucket_reduce_adam: bad arguments");
+    DDPB_REQUIRE(job->world >= 2 && job->world <= DDPB_MAX_PEERS && job->rank >= 0 && job->rank < job->world,
+                 "ddpb_bucket_reduce_adam: world %d / rank %d out of range (2..%d ranks)", job->world, job->rank, DDPB_MAX_PEERS);
+    DDPB_REQUIRE(job->bucket_index >= 0 && job->bucket_index < DDPB_BUCKET_MAX, "ddpb_bucket_reduce_adam: bucket index %d >= %d",
+                 job->bucket_index, DDPB_BUCKET_MAX);
+    DDPB_REQUIRE(job->n >= 0 && job->start >= 0 && job->start % 4 == 0 && job->grads_off % 16 == 0 && job->params_off % 16 == 0 &&
+                     (((uintptr_t)job->m | (uintptr_t)job->v) & 15u) == 0,
+                 "ddpb_bucket_reduce_adam: the bucket must start on a 16-byte boundary of 16-byte aligned buffers");
+    DDPB_REQUIRE(job->ticket >= 1 && job->ticket < 0x7fffffffLL, "ddpb_bucket_reduce_adam: ticket out of range");
+    for (int q = 0; q < job->world; ++q)
+        DDPB_REQUIRE(job->window[q] != nullptr, "ddpb_bucket_reduce_adam: window of rank %d is not mapped", q);
+    cudaStream_t s = (cudaStream_t)stream;
+    int rc = 0;
+    if (job->n > 0) {
+        switch (job->world) {
+            case 2: rc = launch_bucket<2>(*job, s); break;
+            case 3: rc = launch_bucket<3>(*job, s); break;
+            case 4: rc = launch_bucket<4>(*job, s); break;
+            case 5: rc = launch_bucket<5>(*job, s); break;
+            case 6: rc = launch_bucket<6>(*job, s); break;
+            case 7: rc = launch_bucket<7>(*job, s); break;
+            default: rc = launch_bucket<8>(*job, s); break;
+        }
+        if (rc) return rc;
+    }
+    if (job->advance) {
+        advance_state_kernel<<<1, 1, 0, s>>>(job->state);
+        DDPB_CUDA(cudaGetLastError());
+    }
     return 0;
 }

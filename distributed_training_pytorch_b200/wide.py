@@ -6,9 +6,12 @@ the three H x H layers are tcgen05/TMA tf32 GEMMs (csrc/gemm_tf32.cu), the thin 
 streaming kernels (csrc/wide_edges.cu), weight gradients are written straight into the flat
 bucket, and the optimizer is the fused average+Adam pass (28 B/param).  With several ranks the
 flat gradient is cut into buckets (bucket_cap_mb, reverse parameter order like the c10d reducer,
-torch:nn/parallel/distributed.py:1255-1283); each bucket's ncclAllReduce and its Adam pass run on
+torch:nn/parallel/distributed.py:1255-1283); each bucket's all-reduce and its Adam pass run on
 a communication stream as soon as the kernels that produce the bucket have been issued, i.e.
 overlapped with the rest of backward (demo.py:107-111 -> reducer hooks + optimizer.step()).
+On one NVSwitch box that is ONE kernel per bucket (ddpb_bucket_reduce_adam: reduce-scatter by
+pull over peer windows, Adam on the owned shard, all-gather of the new parameters by push);
+DDPB_ALLREDUCE=nccl selects ncclAllReduce + the fused average+Adam pass instead.
 """
 import ctypes
 import os
@@ -60,9 +63,16 @@ class WideBackend:
         self.num_tensors = len(tensors)
         self.P = P = sum(p.numel() for p in tensors)
         assert P == 3 * H * H + 7 * H + 1
+        self.process_group = process_group
+        self.world, self.rank, self.backend_name = 1, 0, None
+        if dist.is_available() and dist.is_initialized():
+            self.world, self.rank = dist.get_world_size(process_group), dist.get_rank(process_group)
+            self.backend_name = dist.get_backend(process_group)
+        self.peer = None
         with torch.cuda.device(dev):
-            self.params = torch.empty(P, dtype=torch.float32, device=dev)
-            self.grads = torch.zeros(P + 1, dtype=torch.float32, device=dev)
+            if not self._map_peer_windows():
+                self.params = torch.empty(P, dtype=torch.float32, device=dev)
+                self.grads = torch.zeros(P + 1, dtype=torch.float32, device=dev)
             self.off = []
             off = 0
             for p in tensors:
@@ -91,11 +101,6 @@ class WideBackend:
         self.loss_host = torch.zeros(LOSS_RING, dtype=torch.float32, pin_memory=True)
         self.loss_bits = self.loss_host.numpy().view(np.uint32)
         self._loss_out = ctypes.c_float()
-        self.process_group = process_group
-        self.world, self.rank, self.backend_name = 1, 0, None
-        if dist.is_available() and dist.is_initialized():
-            self.world, self.rank = dist.get_world_size(process_group), dist.get_rank(process_group)
-            self.backend_name = dist.get_backend(process_group)
         self._sync_replicas()
         # torch's default of 25 MiB costs 15 % here (each bucket pays ~20 us of launch + NCCL latency,
         # DESIGN.md section 7): when the caller names no cap, one bucket per layer
@@ -106,7 +111,11 @@ class WideBackend:
         self.seq = 0
         self.waiting = None
         self.grads_fresh = False
-        self.fused_exchange = False
+        self.ticket = 0
+        if self.peer is not None and len(self.buckets) > _lib.BUCKET_MAX:
+            raise _lib.DdpB200Error(f"{len(self.buckets)} gradient buckets > {_lib.BUCKET_MAX}: raise bucket_cap_mb "
+                                    "or set DDPB_ALLREDUCE=nccl")
+        self.fused_exchange = self.peer is not None
 
     # -- layout ---------------------------------------------------------------------------
     def _w(self, l):          # data_ptr of W_l / b_l in params, of their gradients in grads
@@ -117,6 +126,76 @@ class WideBackend:
 
     def _plan_buckets(self, cap_mb):
         return plan_buckets(self.off, self.P, cap_mb)
+
+    def _map_peer_windows(self):
+        """Several ranks on one NVSwitch box (DDPB_ALLREDUCE=p2p, the default): the flat gradient and
+        parameter buffers live in one IPC-shareable window per rank, [flags | gradients | parameters],
+        mapped into every peer, so that a bucket's all-reduce and its Adam pass are ONE kernel
+        (ddpb_bucket_reduce_adam).  Returns False (nothing allocated) when that is not possible; all
+        ranks decide together."""
+        if (self.world == 1 or self.backend_name != "nccl" or self.world > _lib.MAX_PEERS
+                or os.environ.get("DDPB_ALLREDUCE", "p2p") != "p2p"):
+            return False
+        import socket
+        lib, P = self.lib, self.P
+        up = lambda b: (b + 255) // 256 * 256
+        grads_off = up(_lib.BUCKET_FLAGS_BYTES)
+        params_off = grads_off + up(4 * (P + 4))
+        total = params_off + up(4 * P)
+        mine, handle = ctypes.c_void_p(), ctypes.create_string_buffer(64)
+        _lib.check(lib.ddpb_peer_alloc(total, ctypes.byref(mine), handle), "ddpb_peer_alloc")
+        handles = [None] * self.world
+        dist.all_gather_object(handles, (socket.gethostname(), handle.raw), group=self.process_group)
+        ok = all(h[0] == handles[0][0] for h in handles)
+        mapped = []
+        if ok:
+            for r, (_, raw) in enumerate(handles):
+                if r == self.rank:
+                    mapped.append(mine.value)
+                    continue
+                ptr = ctypes.c_void_p()
+                if lib.ddpb_peer_open(raw, ctypes.byref(ptr)) != 0:
+                    ok = False
+                    break
+                mapped.append(ptr.value)
+        agree = [None] * self.world
+        dist.all_gather_object(agree, bool(ok), group=self.process_group)
+        if not all(agree):
+            for r, ptr in enumerate(mapped):
+                if r != self.rank:
+                    lib.ddpb_peer_close(ptr)
+            lib.ddpb_peer_free(mine)
+            return False
+
+        class _Span:                               # a device range as __cuda_array_interface__ (the window outlives it)
+            def __init__(self, ptr, n):
+                self.__cuda_array_interface__ = {"shape": (n,), "typestr": "<f4", "data": (ptr, False), "version": 2}
+        self.grads = torch.as_tensor(_Span(mine.value + grads_off, P + 1), device=self.device)
+        self.params = torch.as_tensor(_Span(mine.value + params_off, P), device=self.device)
+        if self.grads.data_ptr() != mine.value + grads_off or self.params.data_ptr() != mine.value + params_off:
+            raise _lib.DdpB200Error("could not wrap the peer window as tensors without a copy")
+        self.peer = dict(mine=mine, mapped=mapped, grads_off=grads_off, params_off=params_off)
+        return True
+
+    def _bucket_job(self, index, start, n):
+        """The ddpb_bucket_job of one bucket (built once; ticket / mode / advance change per call)."""
+        h, j = self.hyper, _lib.BucketJob()
+        for r, ptr in enumerate(self.peer["mapped"]):
+            j.window[r] = ptr
+        j.grads_off, j.params_off = self.peer["grads_off"], self.peer["params_off"]
+        j.m, j.v, j.bias_table, j.state = self.m.data_ptr(), self.v.data_ptr(), self.bias_table.data_ptr(), self.state.data_ptr()
+        j.start, j.n, j.bias_table_n = start, n, self.bias_table.shape[0]
+        j.world, j.rank, j.bucket_index = self.world, self.rank, index
+        j.beta1, j.beta2, j.eps, j.grad_scale = h["betas"][0], h["betas"][1], h["eps"], 1.0 / self.world
+        return j
+
+    def _fused_update(self, index, stream, reduce, advance):
+        """One kernel: all-reduce of bucket `index` over the peer windows + Adam on the owned shard +
+        push of the new parameters to every rank."""
+        j = self.bucket_jobs[index]
+        j.ticket, j.mode, j.advance = self.ticket, int(reduce), int(advance)
+        _lib.check(self.lib.ddpb_bucket_reduce_adam(ctypes.byref(j), stream), "ddpb_bucket_reduce_adam")
+        self.engine.launches += 1 + int(advance)
 
     def _sync_replicas(self):
         if self.world == 1:
@@ -140,9 +219,18 @@ class WideBackend:
                 table = _lib.adam_bias_table(hyper["lr"], *hyper["betas"])
                 self.bias_table = torch.from_numpy(table).to(self.device)
         self.sgd_steps = 0
+        self.fused_exchange = self.peer is not None and kind == _lib.OPT_ADAM     # SGD: ncclAllReduce + fused avg+SGD
+        if self.fused_exchange:
+            self.bucket_jobs = [self._bucket_job(i, start, n) for i, (_, start, n) in enumerate(self.buckets)]
 
     def optimizer_state_dict(self):
-        return {"step": int(self.state[0].item()), "exp_avg": self.m, "exp_avg_sq": self.v}
+        m, v = self.m, self.v
+        if self.fused_exchange:
+            # each rank holds Adam state for the shards it owns and zeros elsewhere: the sum is the full state
+            m, v = m.clone(), v.clone()
+            dist.all_reduce(m, group=self.process_group)
+            dist.all_reduce(v, group=self.process_group)
+        return {"step": int(self.state[0].item()), "exp_avg": m, "exp_avg_sq": v}
 
     def discard_pending_backward(self):
         self.waiting = None
@@ -247,12 +335,18 @@ class WideBackend:
             return
         if layer == 4:
             self.sgd_steps += int(with_update)
+            self.ticket += 1
         self.comm_stream.wait_stream(torch.cuda.current_stream(self.device))
         if produced_on is not None:
             self.comm_stream.wait_stream(produced_on)
         cs = self.comm_stream.cuda_stream
-        mine = [bk for bk in self.buckets if bk[0] == layer]
-        for _, start, n in mine:
+        for index, (bucket_layer, start, n) in enumerate(self.buckets):
+            if bucket_layer != layer:
+                continue
+            last = layer == 0 and (start + n) == self.off[2]
+            if self.fused_exchange and with_update:
+                self._fused_update(index, cs, True, last)
+                continue
             ptr = self.grads.data_ptr() + 4 * start
             if self.backend_name == "nccl":
                 _lib.check(self.lib.ddpb_allreduce_sum_f32(self.engine.comm, ptr, n, cs), "ddpb_allreduce_sum_f32")
@@ -262,7 +356,6 @@ class WideBackend:
                     dist.all_reduce(host, group=self.process_group)
                     self.grads[start:start + n].copy_(host)
             if with_update:
-                last = layer == 0 and (start + n) == self.off[2]
                 self._update(start, n, cs, last)
 
     def request_backward(self, loss):
@@ -285,7 +378,14 @@ class WideBackend:
             return
         self.grads_fresh = False
         self.sgd_steps += 1
-        self._update(0, self.P, self.engine.stream(), True)      # gradients are already averaged? no: scaled inside
+        if self.fused_exchange:
+            # the buckets were summed in place by ncclAllReduce during backward: owned shards are
+            # updated and pushed (mode 0), so the sharded Adam state stays the only one
+            self.ticket += 1
+            for index in range(len(self.buckets)):
+                self._fused_update(index, self.engine.stream(), False, index == len(self.buckets) - 1)
+            return
+        self._update(0, self.P, self.engine.stream(), True)      # the 1/W scale is applied inside the pass
 
     # -- results ------------------------------------------------------------------------------
     def read_loss(self, loss):
@@ -313,4 +413,6 @@ class WideBackend:
         return self.out[:B].clone().view(B, 1)
 
     def check_peers(self):
-        pass
+        """Raise if a fused bucket exchange timed out waiting for a peer (state.reserved[0] set by the kernel)."""
+        if self.fused_exchange and int(self.state[2].item()) != 0:
+            raise _lib.DdpB200Error("a peer GPU did not arrive at a gradient bucket in time (fused all-reduce timed out)")

@@ -228,6 +228,42 @@ int ddpb_fused_avg_adam_dev(const float *bucket, float *p, float *m, float *v, i
 int ddpb_fused_avg_sgd(const float *bucket, float *p, float *buf, int64_t n, float grad_scale,
                        double lr, double momentum, int64_t step, void *stream);
 
+/* ---- bucket all-reduce fused with the optimizer, over NVLink peer windows -------------------
+ * Replaces, for one gradient bucket of a large model, the c10d Reducer's ncclAllReduce
+ * (demo.py:107,109 via torch:include/torch/csrc/distributed/c10d/reducer.hpp:276-286) AND
+ * optim.Adam.step on that bucket (demo.py:110-111) by ONE kernel per rank:
+ *   1. wait until every rank has produced the bucket (a flag per rank in the peer windows),
+ *   2. reduce-scatter by pull: rank r sums shard r of the bucket from every rank's gradient buffer
+ *      (16-byte system-scope loads over NVLink), scales by grad_scale = 1/W,
+ *   3. Adam on shard r only (this rank's m and v hold state for its shards; the other entries are
+ *      never touched and stay zero),
+ *   4. all-gather by push: the new parameters of shard r are stored into every rank's parameter
+ *      buffer, then a "done" flag; the kernel ends when every rank's "done" has arrived, so stream
+ *      order makes the next forward see complete parameters.
+ * Every rank's window has the same layout: [flags DDPB_BUCKET_FLAGS_BYTES | gradients | parameters]
+ * at the byte offsets given here; windows come from ddpb_peer_alloc / ddpb_peer_open and start
+ * zeroed.  `ticket` must grow from call to call for a given bucket (the step sequence number).
+ * mode 1 = reduce over the peers; mode 0 = the local gradient buffer already holds the sum
+ * (ncclAllReduce ran, eager backward) and only steps 3-4 are done.  A peer that does not arrive
+ * within ~5 s sets state->reserved[0] = 1 and the kernel gives up.  The optimizer counters are
+ * read from `state`; with advance != 0 they are incremented after the pass (last bucket of a step). */
+#define DDPB_BUCKET_MAX 1024                                         /* buckets per model */
+#define DDPB_BUCKET_FLAGS_BYTES (2 * DDPB_BUCKET_MAX * DDPB_MAX_PEERS * 4 + DDPB_BUCKET_MAX * 4)
+typedef struct ddpb_bucket_job {
+    void *window[DDPB_MAX_PEERS];       /* every rank's window as mapped in this process; [rank] is the own one */
+    int64_t grads_off, params_off;      /* byte offsets of the flat gradient / parameter buffers in a window (16-byte aligned) */
+    float *m, *v;                       /* local Adam state, flat, indexed like the parameters */
+    const float *bias_table;            /* [bias_table_n][2], as for ddpb_fused_avg_adam_dev */
+    ddpb_opt_state *state;
+    int64_t start, n;                   /* the bucket: elements [start, start + n) of the flat buffers, start % 4 == 0 */
+    int64_t ticket;
+    int32_t bias_table_n, world, rank, bucket_index, mode, advance;
+    double beta1, beta2, eps;
+    float grad_scale;                   /* 1 / world */
+    int32_t reserved;
+} ddpb_bucket_job;
+int ddpb_bucket_reduce_adam(const ddpb_bucket_job *job, void *stream);
+
 
 
 /* ---- communicator: NCCL over NVLink --------------------------------------- */

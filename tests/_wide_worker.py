@@ -1,5 +1,6 @@
-"""torchrun worker: the widened model trained data-parallel (bucketed ncclAllReduce + fused
-avg+Adam on the communication stream); dumps the loss curve and final parameters of each rank."""
+"""torchrun worker: the widened model trained data-parallel (per bucket: the fused peer-window
+all-reduce + Adam kernel, or ncclAllReduce + fused avg+Adam with DDPB_ALLREDUCE=nccl, on the
+communication stream); dumps the loss curve and final parameters of each rank."""
 import os
 import sys
 
@@ -36,7 +37,9 @@ def main():
         opt.step()
         losses.append(float(loss.detach().cpu()))
     np.savez(os.path.join(out_dir, f"rank{rank}.npz"), losses=np.asarray(losses, np.float32), init=init,
-             final=model.flat_parameters().cpu().numpy(), buckets=len(model._backend.buckets))
+             final=model.flat_parameters().cpu().numpy(), buckets=len(model._backend.buckets),
+             fused=int(model._backend.fused_exchange), exp_avg=model._backend.optimizer_state_dict()["exp_avg"].cpu().numpy())
+    model._backend.check_peers()
     dist.barrier()
     dist.destroy_process_group()
 

@@ -92,8 +92,9 @@ def test_mpiexec_entry_point_with_the_compat_launcher(tmp_path, golden_dir):
     assert np.max(np.abs(mean - ref) / ref) <= 2e-5
 
 
+@pytest.mark.parametrize("allreduce", ["p2p", "nccl"])
 @pytest.mark.parametrize("cap_mb", [25, 0.05])
-def test_widened_model_data_parallel(tmp_path, cap_mb):
+def test_widened_model_data_parallel(tmp_path, cap_mb, allreduce):
     """Widened model on 2 GPUs: rank 0's weights are broadcast, gradients are averaged bucket by
     bucket (one bucket per layer at 25 MiB, many at 0.05 MiB), replicas stay bit-identical, and the
     run tracks an fp32 PyTorch model trained on the concatenated batch (equal shards: the average
@@ -104,9 +105,12 @@ def test_widened_model_data_parallel(tmp_path, cap_mb):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
            "--master-port", str(_free_port()), os.path.join(ROOT, "tests", "_wide_worker.py"), str(tmp_path), str(H),
            str(B), str(steps), str(cap_mb)]
-    proc = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=600, env=dict(os.environ, OMP_NUM_THREADS="1"))
+    proc = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=600,
+                          env=dict(os.environ, OMP_NUM_THREADS="1", DDPB_ALLREDUCE=allreduce))
     assert proc.returncode == 0, (proc.stdout + proc.stderr)[-4000:]
     r0, r1 = (np.load(os.path.join(tmp_path, f"rank{r}.npz")) for r in range(2))
+    assert int(r0["fused"]) == int(allreduce == "p2p")                  # no silent fallback to the other path
+    assert np.array_equal(r0["exp_avg"], r1["exp_avg"]) and np.any(r0["exp_avg"] != 0)   # gathered optimizer state
     assert np.array_equal(r0["init"], r1["init"])                       # broadcast from rank 0
     assert np.array_equal(r0["final"], r1["final"])                     # replicas stay identical
     assert int(r0["buckets"]) == (5 if cap_mb == 25 else 8)          # 16512-float hidden layers cut at 13104 floats

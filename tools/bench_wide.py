@@ -66,6 +66,8 @@ def sweep(a, world):
                 wire = 2.0 * (world - 1) / world * 4.0 * P
                 print(json.dumps({"hidden": H, "world": world, "local_batch": B, "bucket_cap_mb": cap,
                                   "buckets": len(model._backend.buckets), "ms_per_step": ms,
+                                  "allreduce": "fused peer-window reduce+Adam kernel" if model._backend.fused_exchange
+                                  else "ncclAllReduce + fused avg+Adam",
                                   "samples_per_s": B * world / (ms * 1e-3),
                                   "allreduce_wire_bytes_per_gpu": wire,
                                   "nvlink_floor_ms": wire / 770e9 * 1e3, "hbm_floor_ms": 40.0 * P / 6545.3e9 * 1e3}), flush=True)
