@@ -92,28 +92,25 @@ def test_mpiexec_entry_point_with_the_compat_launcher(tmp_path, golden_dir):
     assert np.max(np.abs(mean - ref) / ref) <= 2e-5
 
 
-@pytest.mark.parametrize("allreduce", ["p2p", "nccl"])
-@pytest.mark.parametrize("cap_mb", [25, 0.05])
-def test_widened_model_data_parallel(tmp_path, cap_mb, allreduce):
-    """Widened model on 2 GPUs: rank 0's weights are broadcast, gradients are averaged bucket by
-    bucket (one bucket per layer at 25 MiB, many at 0.05 MiB), replicas stay bit-identical, and the
-    run tracks an fp32 PyTorch model trained on the concatenated batch (equal shards: the average
-    of the shard gradients IS the gradient of the whole batch) within the tf32 tolerance."""
-    if 2 not in _worlds():
-        pytest.skip("needs 2 GPUs")
+def _widened_run(tmp_path, world, cap_mb, allreduce):
+    """The widened model trained on `world` GPUs against an fp32 PyTorch model trained on the
+    concatenated batch (equal shards: the average of the shard gradients IS the gradient of the whole
+    batch), within the tf32 tolerance."""
     H, B, steps = 128, 64, 12
-    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
-           "--master-port", str(_free_port()), os.path.join(ROOT, "tests", "_wide_worker.py"), str(tmp_path), str(H),
-           str(B), str(steps), str(cap_mb)]
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr",
+           "127.0.0.1", "--master-port", str(_free_port()), os.path.join(ROOT, "tests", "_wide_worker.py"), str(tmp_path),
+           str(H), str(B), str(steps), str(cap_mb)]
     proc = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=600,
                           env=dict(os.environ, OMP_NUM_THREADS="1", DDPB_ALLREDUCE=allreduce))
     assert proc.returncode == 0, (proc.stdout + proc.stderr)[-4000:]
-    r0, r1 = (np.load(os.path.join(tmp_path, f"rank{r}.npz")) for r in range(2))
+    ranks = [np.load(os.path.join(tmp_path, f"rank{r}.npz")) for r in range(world)]
+    r0 = ranks[0]
     assert int(r0["fused"]) == int(allreduce == "p2p")                  # no silent fallback to the other path
-    assert np.array_equal(r0["exp_avg"], r1["exp_avg"]) and np.any(r0["exp_avg"] != 0)   # gathered optimizer state
-    assert np.array_equal(r0["init"], r1["init"])                       # broadcast from rank 0
-    assert np.array_equal(r0["final"], r1["final"])                     # replicas stay identical
-    assert int(r0["buckets"]) == (5 if cap_mb == 25 else 8)          # 16512-float hidden layers cut at 13104 floats
+    assert np.any(r0["exp_avg"] != 0)
+    for r in ranks[1:]:
+        assert np.array_equal(r0["exp_avg"], r["exp_avg"])              # gathered optimizer state
+        assert np.array_equal(r0["init"], r["init"])                    # broadcast from rank 0
+        assert np.array_equal(r0["final"], r["final"])                  # replicas stay identical
     # fp32 reference on the concatenated batch
     torch.backends.cuda.matmul.allow_tf32 = False
     dims = (2, H, H, H, H, 1)
@@ -130,16 +127,39 @@ def test_widened_model_data_parallel(tmp_path, cap_mb, allreduce):
     opt = torch.optim.Adam(twin.parameters(), lr=1e-3)
     g = torch.Generator().manual_seed(7)
     for step in range(steps):
-        z = torch.randn(2 * B, generator=g)
-        y = (0.5 * torch.randn(2 * B, generator=g) + z * z).view(-1, 1).cuda()
+        z = torch.randn(world * B, generator=g)
+        y = (0.5 * torch.randn(world * B, generator=g) + z * z).view(-1, 1).cuda()
         x = torch.stack([z, z], 1).cuda()
         opt.zero_grad()
         per_sample = (twin(x) - y) ** 2
         per_sample.mean().backward()
         opt.step()
-        shard = [per_sample[r * B:(r + 1) * B].mean().item() for r in range(2)]
         tol = 4e-3 if step == 0 else 5e-2          # same weights at step 0; afterwards the two Adam runs drift apart
-        assert abs(r0["losses"][step] - shard[0]) <= tol * shard[0] and abs(r1["losses"][step] - shard[1]) <= tol * shard[1], step
+        for r in range(world):
+            shard = per_sample[r * B:(r + 1) * B].mean().item()
+            assert abs(ranks[r]["losses"][step] - shard) <= tol * shard, (step, r)
     final_t = torch.cat([p.detach().reshape(-1) for p in twin.parameters()]).cpu().numpy()
     delta = np.abs(r0["final"] - final_t)
     assert delta.max() <= 2 * steps * 1e-3 and delta.mean() <= 5e-4
+    return r0
+
+
+@pytest.mark.parametrize("allreduce", ["p2p", "nccl"])
+@pytest.mark.parametrize("cap_mb", [25, 0.05])
+def test_widened_model_data_parallel(tmp_path, cap_mb, allreduce):
+    """Widened model on 2 GPUs: rank 0's weights are broadcast, gradients are averaged bucket by
+    bucket (one bucket per layer at 25 MiB, many at 0.05 MiB) by the fused peer-window kernel or by
+    ncclAllReduce, replicas stay bit-identical, and the run tracks the fp32 model."""
+    if 2 not in _worlds():
+        pytest.skip("needs 2 GPUs")
+    r0 = _widened_run(tmp_path, 2, cap_mb, allreduce)
+    assert int(r0["buckets"]) == (5 if cap_mb == 25 else 8)          # 16512-float hidden layers cut at 13104 floats
+
+
+@pytest.mark.parametrize("world", [4, 8])
+def test_widened_model_fused_exchange_more_ranks(tmp_path, world):
+    """The fused bucket kernel with 4 and 8 ranks (shards of a quarter / an eighth of each bucket, the
+    scalar tail of the last layer's bucket on the last rank)."""
+    if world not in _worlds():
+        pytest.skip(f"needs {world} GPUs")
+    _widened_run(tmp_path, world, 0.05, "p2p")
