@@ -31,6 +31,28 @@ def test_struct_layout_matches_header():
     assert ctypes.sizeof(_lib.OptState) == 32
 
 
+def test_ctypes_structs_agree_with_the_c_compiler(tmp_path):
+    """Every job struct of include/ddp_b200.h, compiled as plain C: size and the offset of each field
+    must be what the ctypes mirrors in _lib.py say (the header is the contract, gcc is the judge)."""
+    import subprocess
+    structs = {"ddpb_toy_job": _lib.ToyJob, "ddpb_seg_job": _lib.SegJob, "ddpb_bucket_job": _lib.BucketJob,
+               "ddpb_opt_state": _lib.OptState}
+    lines = ['#include <stdio.h>', '#include <stddef.h>', '#include "ddp_b200.h"', 'int main(void) {']
+    for cname, cls in structs.items():
+        lines.append(f'  printf("{cname} %zu\\n", sizeof({cname}));')
+        for field, _ in cls._fields_:
+            lines.append(f'  printf("{cname}.{field} %zu\\n", offsetof({cname}, {field}));')
+    lines += ['  return 0;', '}']
+    src, exe = tmp_path / "layout.c", tmp_path / "layout"
+    src.write_text("\n".join(lines))
+    subprocess.run(["gcc", "-std=c99", "-I", os.path.join(ROOT, "include"), "-o", str(exe), str(src)], check=True)
+    out = dict(line.split() for line in subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.splitlines())
+    for cname, cls in structs.items():
+        assert int(out[cname]) == ctypes.sizeof(cls), cname
+        for field, _ in cls._fields_:
+            assert int(out[f"{cname}.{field}"]) == getattr(cls, field).offset, (cname, field)
+
+
 class _Range:
     def __init__(self, n):
         self.n = n
