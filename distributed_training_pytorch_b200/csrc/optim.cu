@@ -205,7 +205,7 @@ bucket_reduce_adam_kernel(const __grid_constant__ ddpb_bucket_job job) {
         if (job.mode) {
 #pragma unroll
             for (int q = 0; q < W; ++q)                      // all peers' loads in flight together; fixed order of the sum
-                part[q] = (q == r) ? __ldcs(grads[q] + i) : ld_sys_f4(grads[q] + i);
+                part[q] = (q == r || (job.reserved & 1)) ? __ldcs(lg + i) : ld_sys_f4(grads[q] + i);
         } else {
             part[0] = __ldcs(lg + i);
         }
@@ -226,7 +226,7 @@ bucket_reduce_adam_kernel(const __grid_constant__ ddpb_bucket_job job) {
 #pragma unroll
         for (int q = 0; q < W; ++q) {
             if (q == r) params[q][i] = pp;
-            else st_sys_f4(params[q] + i, pp);
+            else if (!(job.reserved & 2)) st_sys_f4(params[q] + i, pp);
         }
     }
     // the 1-3 elements after the last full group of four (only the last layer's bucket has them)
@@ -320,7 +320,10 @@ namespace {
 template <int W>
 int launch_bucket(const ddpb_bucket_job &job, cudaStream_t stream) {
     const long long n4 = job.n >> 2, per = (n4 + W - 1) / W;
-    bucket_reduce_adam_kernel<W><<<stream_grid(per * 4, 4), 256, 0, stream>>>(job);
+    int grid = stream_grid(per * 4, 4);
+    const int cap = (job.reserved >> 8) & 0xffff;            // diagnostic: cap the grid
+    if (cap && grid > cap) grid = cap;
+    bucket_reduce_adam_kernel<W><<<grid, 256, 0, stream>>>(job);
     DDPB_CUDA(cudaGetLastError());
     return 0;
 }

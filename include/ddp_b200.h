@@ -260,7 +260,9 @@ typedef struct ddpb_bucket_job {
     int32_t bias_table_n, world, rank, bucket_index, mode, advance;
     double beta1, beta2, eps;
     float grad_scale;                   /* 1 / world */
-    int32_t reserved;
+    int32_t reserved;                   /* 0.  Diagnostic bits for tools/bench_wide.py (results are then WRONG on
+                                         * purpose): 1 = read the local buffer instead of the peers', 2 = do not
+                                         * push parameters, bits 8..23 = cap on the grid */
 } ddpb_bucket_job;
 int ddpb_bucket_reduce_adam(const ddpb_bucket_job *job, void *stream);
 

@@ -61,11 +61,32 @@ def sweep(a, world):
             t = torch.tensor([e0.elapsed_time(e1) / a.steps], dtype=torch.float64)
             dist.all_reduce(t, op=dist.ReduceOp.MAX, group=side)
             P = model._backend.P
+            # each bucket's fused all-reduce + Adam kernel on its own (nothing else on the GPU): is the
+            # kernel at wire speed, or is it the overlap with backward that costs?
+            alone = None
+            be = model._backend
+            if be.fused_exchange:
+                alone = []
+                cs = torch.cuda.current_stream().cuda_stream
+                for index, (layer, start, n) in enumerate(be.buckets):
+                    be.bucket_jobs[index].reserved = int(os.environ.get("DDPB_BUCKET_DIAG", "0"))
+                    ts = []
+                    for rep in range(5):
+                        dist.barrier(); torch.cuda.synchronize()
+                        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                        be.ticket += 1
+                        a0.record(); be._fused_update(index, cs, True, False); a1.record(); torch.cuda.synchronize()
+                        ts.append(a0.elapsed_time(a1) * 1e3)
+                    tk = torch.tensor([sorted(ts)[2]], dtype=torch.float64)
+                    dist.all_reduce(tk, op=dist.ReduceOp.MAX, group=side)
+                    alone.append({"layer": layer, "floats": n, "us": round(float(tk), 1),
+                                  "nvlink_in_gbs": round(4.0 * n * (world - 1) / world / float(tk) / 1e3, 1)})
             if rank == 0:
                 ms = float(t)
                 wire = 2.0 * (world - 1) / world * 4.0 * P
                 print(json.dumps({"hidden": H, "world": world, "local_batch": B, "bucket_cap_mb": cap,
                                   "buckets": len(model._backend.buckets), "ms_per_step": ms,
+                                  "bucket_kernels_alone": alone,
                                   "allreduce": "fused peer-window reduce+Adam kernel" if model._backend.fused_exchange
                                   else "ncclAllReduce + fused avg+Adam",
                                   "samples_per_s": B * world / (ms * 1e-3),
