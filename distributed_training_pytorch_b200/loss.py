@@ -46,6 +46,50 @@ class Loss:
     def cpu(self):
         return self.detach().cpu()
 
+    def __add__(self, other):
+        if isinstance(other, Loss):
+            return LossSum([self, other])
+        if isinstance(other, LossSum):
+            return LossSum([self] + other.terms)
+        return NotImplemented
+
+    def __radd__(self, other):           # sum([l_X, l_Y]) starts from 0
+        return self if (isinstance(other, (int, float)) and other == 0) else NotImplemented
+
+
+class LossSum:
+    """loss_X + loss_Y (demo_pytorch_lightning.py:27-33: one summed loss, one backward, then every
+    optimizer steps).  d(sum)/d(loss_k) = 1, so backward() is each term's backward(); the value is the
+    sum of the terms' values."""
+
+    def __init__(self, terms):
+        self.terms = list(terms)
+
+    def __add__(self, other):
+        if isinstance(other, Loss):
+            return LossSum(self.terms + [other])
+        if isinstance(other, LossSum):
+            return LossSum(self.terms + other.terms)
+        return NotImplemented
+
+    __radd__ = __add__
+
+    def backward(self):
+        for t in self.terms:
+            t.backward()
+
+    def detach(self):
+        return self
+
+    def cpu(self):
+        return torch.stack([t.detach().cpu() for t in self.terms]).sum()
+
+    def item(self):
+        return float(self.cpu())
+
+    def __float__(self):
+        return self.item()
+
 
 class LossValue:
     """Result of loss.detach(): still lazy; .cpu() is the synchronisation point

@@ -16,7 +16,7 @@ from distributed_training_pytorch_b200 import DistributedDataParallel as DDP
 pytestmark = pytest.mark.gpu
 
 
-def _loop(iters, device_resident=False, lazy=None, plain_tensors=False):
+def _loop(iters, device_resident=False, lazy=None, plain_tensors=False, summed=False):
     torch.manual_seed(1234)
     mx, my = ToyModel(), ToyModel()
     data = ToyData()
@@ -34,8 +34,13 @@ def _loop(iters, device_resident=False, lazy=None, plain_tensors=False):
             x, t = x.cuda(), t.cuda()
             if plain_tensors:
                 x, t = x.clone(), t.clone()
-            l_X = loss(model_X(x), t); l_X.backward()
-            l_Y = loss(model_Y(x), t); l_Y.backward()
+            if summed:                       # demo_pytorch_lightning.py:27-33: one summed loss, one backward
+                l_X, l_Y = loss(model_X(x), t), loss(model_Y(x), t)
+                total = l_X + l_Y
+                total.backward()
+            else:
+                l_X = loss(model_X(x), t); l_X.backward()
+                l_Y = loss(model_Y(x), t); l_Y.backward()
             opt_X.step(); opt_Y.step()
             losses.append((float(l_X.detach().cpu()), float(l_Y.detach().cpu())))
             it += 1
@@ -59,6 +64,26 @@ def test_frontend_reproduces_reference_curve(golden_dir, mode):
     w0 = model_X.module.layers[0].weight
     assert w0.data_ptr() == model_X.flat_parameters().data_ptr() and w0.grad is not None
     assert list(model_X.state_dict())[0] == "module.layers.0.weight"
+
+
+def test_summed_loss_single_backward():
+    """(loss_X + loss_Y).backward() then both optimizers (the Lightning variant of the reference,
+    demo_pytorch_lightning.py:27-38) is the same computation as two backward calls: identical
+    parameters, still one launch per iteration, and the sum reads back as the sum."""
+    from distributed_training_pytorch_b200.engine import engine_for
+    a, ax, ay = _loop(20)
+    before = engine_for(0).launches
+    b, bx, by = _loop(20, summed=True)
+    assert engine_for(0).launches - before == 20
+    assert np.array_equal(a, b)
+    assert torch.equal(ax.flat_parameters(), bx.flat_parameters()) and torch.equal(ay.flat_parameters(), by.flat_parameters())
+    x = torch.randn(64, 1, device="cuda").repeat(1, 2).contiguous()
+    t = torch.randn(64, 1, device="cuda")
+    loss = nn.MSELoss()
+    l1, l2 = loss(bx(x), t), loss(by(x), t)
+    total = sum([l1, l2])
+    total.backward()
+    assert abs(float(total.detach().cpu()) - (float(l1.detach().cpu()) + float(l2.detach().cpu()))) <= 1e-6
 
 
 def test_one_launch_per_iteration_when_lazy():
