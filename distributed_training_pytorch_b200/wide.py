@@ -412,6 +412,22 @@ class WideBackend:
         _lib.check(lib.ddpb_wide_last_fwd(self.act[3].data_ptr(), w, b, None, None, self.out.data_ptr(), None, None, B, H, stream))
         return self.out[:B].clone().view(B, 1)
 
+    def close(self):
+        """Collective: unmap the peers' windows and free this rank's (every rank calls it, after which
+        the module's parameters and gradients must not be used).  Without it the windows live until
+        the process exits."""
+        if self.peer is None:
+            return
+        torch.cuda.synchronize(self.device)
+        dist.barrier(group=self.process_group)               # nobody is still inside a bucket kernel
+        for r, ptr in enumerate(self.peer["mapped"]):
+            if r != self.rank:
+                self.lib.ddpb_peer_close(ptr)
+        dist.barrier(group=self.process_group)               # every mapping of my window is closed
+        self.lib.ddpb_peer_free(self.peer["mine"])
+        self.peer, self.fused_exchange = None, False
+        self.params = self.grads = None
+
     def check_peers(self):
         """Raise if a fused bucket exchange timed out waiting for a peer (state.reserved[0] set by the kernel)."""
         if self.fused_exchange and int(self.state[2].item()) != 0:

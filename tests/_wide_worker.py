@@ -40,6 +40,7 @@ def main():
              final=model.flat_parameters().cpu().numpy(), buckets=len(model._backend.buckets),
              fused=int(model._backend.fused_exchange), exp_avg=model._backend.optimizer_state_dict()["exp_avg"].cpu().numpy())
     model._backend.check_peers()
+    model._backend.close()                        # collective teardown of the peer windows (no-op on the NCCL path)
     dist.barrier()
     dist.destroy_process_group()
 

@@ -92,6 +92,7 @@ def sweep(a, world):
                                   "samples_per_s": B * world / (ms * 1e-3),
                                   "allreduce_wire_bytes_per_gpu": wire,
                                   "nvlink_floor_ms": wire / 770e9 * 1e3, "hbm_floor_ms": 40.0 * P / 6545.3e9 * 1e3}), flush=True)
+            model._backend.close()                           # frees the peer windows of this model (collective)
             del model, opt
             torch.cuda.empty_cache()
     dist.destroy_process_group()
