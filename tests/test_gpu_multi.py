@@ -163,3 +163,76 @@ def test_widened_model_fused_exchange_more_ranks(tmp_path, world):
     if world not in _worlds():
         pytest.skip(f"needs {world} GPUs")
     _widened_run(tmp_path, world, 0.05, "p2p")
+
+
+@pytest.mark.parametrize("mode", [1, 0])
+def test_bucket_reduce_adam_bit_exact_against_the_oracle(oracle, native_lib, mode):
+    """ddpb_bucket_reduce_adam through the C ABI, two GPUs driven from ONE process (plain device
+    buffers as the two windows, peer access enabled): after three steps the parameters of both ranks,
+    and each rank's shard of the Adam state, are BIT-identical to the CPU oracle's `sum in rank
+    order -> x 1/W -> Adam` (oracle/ddp_oracle.c), nothing outside the bucket is touched, and the
+    state of the shards a rank does not own stays zero."""
+    import ctypes
+    from distributed_training_pytorch_b200 import _lib
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    _lib.check(native_lib.ddpb_enable_peer(0, 1), "ddpb_enable_peer")
+    W, P, start, n = 2, 10007, 16, 9987                    # n % 4 == 3: the scalar tail is rank 1's
+    up = lambda b: (b + 255) // 256 * 256
+    grads_off = up(_lib.BUCKET_FLAGS_BYTES)
+    params_off = grads_off + up(4 * (P + 4))
+    total = params_off + up(4 * P)
+    rng = np.random.default_rng(3)
+    p_ref = rng.standard_normal(P).astype(np.float32)
+    m_ref, v_ref = np.zeros(P, np.float32), np.zeros(P, np.float32)
+    win, grads, params, m, v, state, table, jobs = [], [], [], [], [], [], [], []
+    for d in range(W):
+        with torch.cuda.device(d):
+            w = torch.zeros(total, dtype=torch.uint8, device=f"cuda:{d}")
+            win.append(w)
+            grads.append(w[grads_off:grads_off + 4 * P].view(torch.float32))
+            params.append(w[params_off:params_off + 4 * P].view(torch.float32))
+            params[d].copy_(torch.from_numpy(p_ref))
+            m.append(torch.zeros(P, device=f"cuda:{d}")); v.append(torch.zeros(P, device=f"cuda:{d}"))
+            state.append(torch.zeros(4, dtype=torch.int64, device=f"cuda:{d}"))
+            table.append(torch.from_numpy(_lib.adam_bias_table(1e-3, 0.9, 0.999)).to(f"cuda:{d}"))
+    for d in range(W):
+        j = _lib.BucketJob()
+        for q in range(W):
+            j.window[q] = win[q].data_ptr()
+        j.grads_off, j.params_off = grads_off, params_off
+        j.m, j.v, j.bias_table, j.state = m[d].data_ptr(), v[d].data_ptr(), table[d].data_ptr(), state[d].data_ptr()
+        j.start, j.n, j.bias_table_n = start, n, table[d].shape[0]
+        j.world, j.rank, j.bucket_index, j.mode, j.advance = W, d, 5, mode, 1
+        j.beta1, j.beta2, j.eps, j.grad_scale = 0.9, 0.999, 1e-8, 1.0 / W
+        jobs.append(j)
+    for step in range(1, 4):
+        g = [(rng.standard_normal(P) * 10 ** rng.uniform(-4, 1)).astype(np.float32) for _ in range(W)]
+        total_g = g[0] + g[1]                                                # float32, rank order
+        for d in range(W):
+            grads[d].copy_(torch.from_numpy(g[d] if mode else total_g))    # mode 0: already summed in place
+        for d in range(W):
+            torch.cuda.synchronize(d)
+        for d in range(W):                                                   # both kernels in flight: they wait for each other
+            with torch.cuda.device(d):
+                jobs[d].ticket = step
+                _lib.check(native_lib.ddpb_bucket_reduce_adam(ctypes.byref(jobs[d]), torch.cuda.current_stream(d).cuda_stream),
+                           "ddpb_bucket_reduce_adam")
+        for d in range(W):
+            torch.cuda.synchronize(d)
+        sl = slice(start, start + n)
+        pb, mb, vb = p_ref[sl].copy(), m_ref[sl].copy(), v_ref[sl].copy()
+        oracle.adam_step(pb, total_g[sl] * np.float32(1.0 / W), mb, vb, step)
+        p_ref[sl], m_ref[sl], v_ref[sl] = pb, mb, vb
+    n4 = n >> 2
+    per = (n4 + W - 1) // W
+    owned = [slice(start, start + 4 * per), slice(start + 4 * per, start + n)]
+    for d in range(W):
+        assert np.array_equal(params[d].cpu().numpy(), p_ref), d            # whole buffer: bucket updated, rest untouched
+        got_m, got_v = m[d].cpu().numpy(), v[d].cpu().numpy()
+        assert np.array_equal(got_m[owned[d]], m_ref[owned[d]]) and np.array_equal(got_v[owned[d]], v_ref[owned[d]])
+        other = owned[1 - d]
+        assert not got_m[other].any() and not got_v[other].any()
+        assert not got_m[:start].any() and not got_m[start + n:].any()
+        st = state[d].cpu().numpy()
+        assert st[0] == 3 and st[2] == 0                                    # three steps, no peer time-out
