@@ -13,8 +13,9 @@ small shim that
   * records what wandb.log receives (demo.py:120-121) and the final parameters.
 
 Usage:  python tests/golden/make_golden.py            # spawns torchrun for W=1,2,4,8
+        python tests/golden/make_golden.py standard   # only ref_w2_standard.npz (--dataloader=standard, W=2)
 Outputs: ref_w{W}.npz (loss curves, initial / step-200 / final parameters), dataset.npz,
-         sampler.npz, meta.json.
+         sampler.npz, meta.json; ref_w2_standard.npz.
 """
 import hashlib
 import json
@@ -88,7 +89,7 @@ def worker():
 
     demo.setup_distributed, demo.training_demo, demo.get_dataloader = setup, loop, loader
     torch.manual_seed(SEED)
-    sys.argv = [sys.argv[0], "--backend=gloo", "--torchrun", "--dry_run"]
+    sys.argv = [sys.argv[0], "--backend=gloo", "--torchrun", "--dry_run"] + os.environ.get("GOLDEN_ARGS", "").split()
     demo.main()
     captured.pop("models")
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
@@ -99,6 +100,33 @@ def worker():
 
 def sha(a):
     return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()[:16]
+
+
+def _run_reference(world, extra_args=""):
+    """One run of the reference under torchrun; returns the per-rank captures."""
+    import shutil
+    tmp = os.path.join(HERE, "..", "..", "gpurun_out", f"golden_tmp_w{world}")      # scratch inside the repo (git-ignored)
+    shutil.rmtree(tmp, ignore_errors=True)
+    os.makedirs(tmp)
+    env = dict(os.environ, GOLDEN_TMP=tmp, OMP_NUM_THREADS="1", GOLDEN_WORKER="1", GOLDEN_ARGS=extra_args)
+    subprocess.run([sys.executable, "-m", "torch.distributed.run", "--standalone", "--local-addr", "127.0.0.1",
+                    f"--nproc_per_node={world}", os.path.abspath(__file__)], check=True, env=env, cwd=tmp)
+    ranks = [dict(np.load(os.path.join(tmp, f"w{world}_r{r}.npz"))) for r in range(world)]
+    shutil.rmtree(tmp, ignore_errors=True)
+    return ranks
+
+
+def driver_standard():
+    """--dataloader=standard at W=2 (demo.py:149-154): no sampler, every rank walks all 512 samples in
+    order (2 steps per epoch, identical batches on both ranks)."""
+    ranks = _run_reference(2, "--dataloader=standard")
+    r0 = ranks[0]
+    assert np.array_equal(ranks[1]["final_X"], r0["final_X"]) and np.array_equal(ranks[1]["final_Y"], r0["final_Y"])
+    np.savez(os.path.join(HERE, "ref_w2_standard.npz"),
+             lossX=r0["lossX"].astype(np.float32), lossY=r0["lossY"].astype(np.float32),
+             init_X=r0["init_X"], init_Y=r0["init_Y"], final_X=r0["final_X"], final_Y=r0["final_Y"],
+             mid_X=r0["mid_X"], mid_Y=r0["mid_Y"], mid_step=np.int64(MID))
+    print("ref_w2_standard.npz: loss0", float(r0["lossX"][0]), float(r0["lossY"][0]), "final_X sha", sha(r0["final_X"]))
 
 
 def driver():
@@ -161,4 +189,9 @@ def driver():
 
 
 if __name__ == "__main__":
-    worker() if os.environ.get("GOLDEN_WORKER") else driver()
+    if os.environ.get("GOLDEN_WORKER"):
+        worker()
+    elif sys.argv[1:] == ["standard"]:
+        driver_standard()
+    else:
+        driver()

@@ -64,13 +64,17 @@ def test_single_rank_demo_entry_point(tmp_path, golden_dir):
     assert np.max(np.abs(ranks[0]["px"] - g["mid_X"])) <= 2e-5
 
 
-def test_standard_dataloader_mode(tmp_path):
-    """--dataloader standard: every rank walks the whole dataset in order (demo.py:149-154)."""
+def test_standard_dataloader_mode(tmp_path, golden_dir):
+    """--dataloader standard: every rank walks the whole dataset in order (demo.py:149-154); pinned
+    by the reference's own W=2 run in that mode (tests/golden/ref_w2_standard.npz)."""
     if 2 not in _worlds():
         pytest.skip("needs 2 GPUs")
     ranks = _run_demo(tmp_path, 2, "p2p", ("--backend=nccl", "--torchrun", "--dry_run", "--dataloader=standard"))
-    assert np.array_equal(ranks[0]["px"], ranks[1]["px"])
-    assert np.isfinite(ranks[0]["losses"]).all() and ranks[0]["losses"][-1, 0] < ranks[0]["losses"][0, 0]
+    assert np.array_equal(ranks[0]["px"], ranks[1]["px"]) and np.array_equal(ranks[0]["py"], ranks[1]["py"])
+    g = np.load(os.path.join(golden_dir, "ref_w2_standard.npz"))
+    ref = np.stack([g["lossX"], g["lossY"]], axis=1)[:200]
+    assert np.max(np.abs(ranks[0]["losses"] - ref) / ref) <= 2e-5
+    assert np.max(np.abs(ranks[0]["px"] - g["mid_X"])) <= 2e-5 and np.max(np.abs(ranks[0]["py"] - g["mid_Y"])) <= 2e-5
 
 
 def test_mpiexec_entry_point_with_the_compat_launcher(tmp_path, golden_dir):

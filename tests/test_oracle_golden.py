@@ -140,3 +140,17 @@ def test_training_loop_against_reference_run(oracle, golden_dir, world):
     assert rel[:500].max() <= 2e-5
     assert rel.max() <= 1e-2
     assert abs(float(losses[-1, 0]) - float(ref[-1, 0])) < 1e-3
+
+
+def test_standard_dataloader_loop_against_reference_run(oracle, golden_dir):
+    """--dataloader=standard (demo.py:149-154), W=2: no sampler, both ranks walk all 512 samples in
+    order, so the averaged gradient is the gradient of the shared batch.  Pinned by the reference's
+    own run (tests/golden/ref_w2_standard.npz)."""
+    g = np.load(os.path.join(golden_dir, "ref_w2_standard.npz"))
+    d = np.load(os.path.join(golden_dir, "dataset.npz"))
+    mid = int(g["mid_step"])
+    p0 = np.stack([g["init_X"], g["init_Y"]])
+    p_mid, losses = oracle.train_loop(p0, TOY_DIMS, d["x"], d["y"], 2, mid, mode="standard")
+    assert np.max(np.abs(p_mid - np.stack([g["mid_X"], g["mid_Y"]]))) <= 2e-5
+    ref = np.stack([g["lossX"], g["lossY"]], axis=1)[:mid]
+    assert (np.abs(losses - ref) / np.abs(ref)).max() <= 2e-5

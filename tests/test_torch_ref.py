@@ -22,3 +22,14 @@ def test_torch_ref_is_bit_identical_to_the_reference_run(golden_dir):
     assert np.array_equal(losses[:, 0], g["lossX"][:200])
     assert np.array_equal(losses[:, 1], g["lossY"][:200])
     assert np.array_equal(res["params"][0], g["mid_X"]) and np.array_equal(res["params"][1], g["mid_Y"])
+
+
+def test_torch_ref_standard_dataloader_single_rank_equals_the_two_rank_reference_run(golden_dir):
+    """--dataloader=standard: every rank sees the same batches, so averaging over ranks changes
+    nothing but rounding (x 1/2 then + is exact): a single-rank torch_ref run in standard mode
+    reproduces the reference's W=2 standard run bit for bit."""
+    g = np.load(os.path.join(golden_dir, "ref_w2_standard.npz"))
+    res = torch_ref.run(1, 0, _free_port(), iters=200, warmup=0, mode="standard", record=True)
+    losses = np.asarray(res["losses"], np.float32)
+    assert np.array_equal(losses[:, 0], g["lossX"][:200]) and np.array_equal(losses[:, 1], g["lossY"][:200])
+    assert np.array_equal(res["params"][0], g["mid_X"]) and np.array_equal(res["params"][1], g["mid_Y"])
