@@ -14,6 +14,7 @@ small shim that
 
 Usage:  python tests/golden/make_golden.py            # spawns torchrun for W=1,2,4,8
         python tests/golden/make_golden.py standard   # only ref_w2_standard.npz (--dataloader=standard, W=2)
+        python tests/golden/make_golden.py modelparallel   # only ref_model_parallel_w1.npz (demo_one_model_multi_gpu.py)
 Outputs: ref_w{W}.npz (loss curves, initial / step-200 / final parameters), dataset.npz,
          sampler.npz, meta.json; ref_w2_standard.npz.
 """
@@ -96,6 +97,57 @@ def worker():
     np.savez(os.path.join(os.environ["GOLDEN_TMP"], f"w{world}_r{rank}.npz"),
              lossX=np.asarray(logged["loss/lossX"], np.float64),
              lossY=np.asarray(logged["loss/lossY"], np.float64), **captured)
+
+
+def worker_model_parallel():
+    """demo_one_model_multi_gpu.py (one model split over two devices, one Adam) executed as a script
+    on CPU: Module.to / Tensor.to with an integer device become identities, device_count() says 2
+    (its assert at :89), pin_memory is off, wandb is captured."""
+    import runpy
+    import torch
+    sys.path.insert(0, REF)
+    torch.cuda.device_count = lambda: 2
+    stock_module_to, stock_tensor_to = torch.nn.Module.to, torch.Tensor.to
+    torch.nn.Module.to = lambda self, *a, **k: self if (a and isinstance(a[0], int)) else stock_module_to(self, *a, **k)
+    torch.Tensor.to = lambda self, *a, **k: self if (a and isinstance(a[0], int)) else stock_tensor_to(self, *a, **k)
+    import torch.nn.parallel as tnp
+    import torch.utils.data as tud
+    import toy_model_and_data
+    import wandb
+    stock_ddp, stock_loader, stock_data = tnp.DistributedDataParallel, tud.DataLoader, toy_model_and_data.ToyData
+    captured, logged = {}, []
+
+    class HostDDP(stock_ddp):
+        def __init__(self, module, device_ids=None, **kw):
+            super().__init__(module, device_ids=None, **kw)
+            captured["model"] = self
+            captured["init"] = _flat(self.module)
+
+    class RecordedData(stock_data):
+        def __init__(self):
+            super().__init__()
+            captured["data_x"] = torch.stack(self.data).numpy().copy()
+            captured["data_y"] = torch.stack(self.y).numpy().copy()
+
+    tnp.DistributedDataParallel = HostDDP
+    tud.DataLoader = lambda *a, **k: stock_loader(*a, **{**k, "pin_memory": False})
+    toy_model_and_data.ToyData = RecordedData
+
+    def _log(d, **k):
+        logged.append(float(d["loss/loss"]))
+        if len(logged) == MID:
+            captured["mid"] = _flat(captured["model"].module)
+
+    wandb.init = lambda *a, **k: None
+    wandb.log = _log
+    wandb.Settings = lambda *a, **k: None
+    torch.manual_seed(SEED)
+    sys.argv = [os.path.join(REF, "demo_one_model_multi_gpu.py"), "--backend=gloo", "--torchrun", "--dry_run"]
+    runpy.run_path(sys.argv[0], run_name="__main__")
+    model = captured.pop("model")
+    np.savez(os.path.join(HERE, "ref_model_parallel_w1.npz"), loss=np.asarray(logged, np.float32),
+             final=_flat(model.module), mid_step=np.int64(MID), **captured)
+    print("ref_model_parallel_w1.npz: loss0", logged[0], "loss999", logged[-1], "final sha", sha(_flat(model.module)))
 
 
 def sha(a):
@@ -191,7 +243,15 @@ def driver():
 if __name__ == "__main__":
     if os.environ.get("GOLDEN_WORKER"):
         worker()
+    elif os.environ.get("GOLDEN_MP_WORKER"):
+        worker_model_parallel()
     elif sys.argv[1:] == ["standard"]:
         driver_standard()
+    elif sys.argv[1:] == ["modelparallel"]:
+        scratch = os.path.join(HERE, "..", "..", "gpurun_out", "golden_tmp_mp")     # wandb dry-run files land in the cwd
+        os.makedirs(scratch, exist_ok=True)
+        subprocess.run([sys.executable, "-m", "torch.distributed.run", "--standalone", "--local-addr", "127.0.0.1",
+                        "--nproc_per_node=1", os.path.abspath(__file__)], check=True, cwd=scratch,
+                       env=dict(os.environ, OMP_NUM_THREADS="1", GOLDEN_MP_WORKER="1"))
     else:
         driver()

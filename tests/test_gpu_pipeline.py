@@ -135,3 +135,7 @@ def test_model_parallel_demo_entry_point(tmp_path, oracle):
     p_ref, losses_ref = oracle.train_loop(init[None], TOY_DIMS, data.x_dense.numpy(), data.y_dense.numpy(), 1, 100)
     assert np.max(np.abs(out["losses"] - losses_ref[:, 0]) / losses_ref[:, 0]) <= 1e-5
     assert np.max(np.abs(out["p"] - p_ref[0])) <= 1e-5
+    # and the reference's own run of demo_one_model_multi_gpu.py (tests/golden/make_golden.py modelparallel)
+    g = np.load(os.path.join(ROOT, "tests", "golden", "ref_model_parallel_w1.npz"))
+    assert np.array_equal(init, g["init"]) and np.array_equal(data.x_dense.numpy(), g["data_x"])
+    assert np.max(np.abs(out["losses"] - g["loss"][:100]) / g["loss"][:100]) <= 2e-5

@@ -154,3 +154,16 @@ def test_standard_dataloader_loop_against_reference_run(oracle, golden_dir):
     assert np.max(np.abs(p_mid - np.stack([g["mid_X"], g["mid_Y"]]))) <= 2e-5
     ref = np.stack([g["lossX"], g["lossY"]], axis=1)[:mid]
     assert (np.abs(losses - ref) / np.abs(ref)).max() <= 2e-5
+
+
+def test_model_parallel_demo_loop_against_reference_run(oracle, golden_dir):
+    """demo_one_model_multi_gpu.py (one model in two stages, a single Adam): the reference's own run
+    under the CPU shim of make_golden.py (`modelparallel`), against the oracle's loop with one model.
+    Splitting the layer stack over two devices does not change the arithmetic."""
+    g = np.load(os.path.join(golden_dir, "ref_model_parallel_w1.npz"))
+    mid = int(g["mid_step"])
+    p_mid, losses = oracle.train_loop(g["init"][None], TOY_DIMS, g["data_x"], g["data_y"], 1, mid)
+    assert np.max(np.abs(p_mid[0] - g["mid"])) <= 2e-5
+    assert (np.abs(losses[:, 0] - g["loss"][:mid]) / np.abs(g["loss"][:mid])).max() <= 2e-5
+    # same seed, same constructor order as ToyModel: the split model starts from model X's weights
+    assert np.array_equal(g["init"], np.load(os.path.join(golden_dir, "ref_w1.npz"))["init_X"])
