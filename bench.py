@@ -156,11 +156,9 @@ def reference_arm(args):
 # our arm
 # --------------------------------------------------------------------------------------
 def ours(args):
-    import numpy as np
     import torch
     import torch.distributed as dist
 
-    import distributed_training_pytorch_b200 as b200
     from distributed_training_pytorch_b200 import DataLoader, DistributedSampler, ToyData, ToyModel, _lib, nn, optim
     from distributed_training_pytorch_b200 import DistributedDataParallel as DDP
     from distributed_training_pytorch_b200.engine import engine_for

@@ -17,7 +17,6 @@ import torch.distributed as dist
 from torch.distributed.elastic.multiprocessing.errors import record
 from tqdm import tqdm
 
-import distributed_training_pytorch_b200 as b200
 from distributed_training_pytorch_b200 import DataLoader, DistributedSampler, ToyData, ToyModel, bootstrap, nn, optim
 from distributed_training_pytorch_b200 import DistributedDataParallel as DDP
 from distributed_training_pytorch_b200.argument_parser import get_args

@@ -8,7 +8,6 @@ come out as HostBatch objects whose .cuda() is one async H2D copy of the whole (
 block.  With device_resident=True (or DDPB_DEVICE_DATA=1) the dataset and the sampler's
 index rows live in HBM and a batch is just an index-row handle (no per-step copies).
 """
-import ctypes
 import math
 import os
 

@@ -3,8 +3,6 @@ object with .backward() and .detach().cpu().  Nothing is computed when it is bui
 mean-squared error comes out of the same fused kernel that produces the gradients."""
 import torch
 
-from . import _lib
-
 
 class MSELoss:
     def __init__(self, reduction="mean"):

@@ -1,5 +1,4 @@
 """Helpers for the -m gpu tests: call the C ABI on torch-owned device buffers."""
-import ctypes
 
 import numpy as np
 import torch

@@ -6,7 +6,6 @@ Tolerance: operands are truncated to tf32 (10 explicit mantissa bits, relative e
 per operand) and accumulated in fp32, so an inner product of length K with terms of magnitude
 |a||b| errs by about 2^-10 * sqrt(K) * rms(|a||b|); the tests allow 4e-3 of the output's max
 magnitude (measured: ~5e-4)."""
-import numpy as np
 import pytest
 import torch
 
