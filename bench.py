@@ -118,7 +118,13 @@ def run_cpu_reference(world, iters, warmup):
     """Spawns the W-rank gloo CPU job (one process per rank, OMP_NUM_THREADS=1 like the
     reference's launch scripts) and returns the seconds rank 0 measured for `iters` steps."""
     port = free_port()
-    env = dict(os.environ, OMP_NUM_THREADS="1", MKL_NUM_THREADS="1", CUDA_VISIBLE_DEVICES="")
+    # Not the launcher's environment: under torch.distributed.run, TORCHELASTIC_USE_AGENT_STORE makes
+    # init_process_group("tcp://...") expect the agent's store instead of starting its own, and the
+    # job would wait for ever.
+    launcher = ("RANK", "LOCAL_RANK", "WORLD_SIZE", "LOCAL_WORLD_SIZE", "GROUP_RANK", "GROUP_WORLD_SIZE", "ROLE_RANK",
+                "ROLE_WORLD_SIZE", "ROLE_NAME", "MASTER_ADDR", "MASTER_PORT")
+    env = {k: v for k, v in os.environ.items() if k not in launcher and not k.startswith(("TORCHELASTIC_", "TORCH_NCCL_"))}
+    env.update(OMP_NUM_THREADS="1", MKL_NUM_THREADS="1", CUDA_VISIBLE_DEVICES="")
     script = os.path.join(ROOT, "oracle", "torch_ref.py")
     procs = [subprocess.Popen([sys.executable, script, "--world", str(world), "--rank", str(r), "--port", str(port),
                                "--iters", str(iters), "--warmup", str(warmup)], env=env, cwd=ROOT,
