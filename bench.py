@@ -161,6 +161,318 @@ def reference_arm(args):
 # --------------------------------------------------------------------------------------
 # our arm
 # --------------------------------------------------------------------------------------
+class Ctx:
+    pass
+
+
+def ncu_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of toy_step_kernel, from the newest
+    committed `ncu --set full` raw page under profiles/ (cold caches: ncu flushes between replays)."""
+    import csv
+    import glob
+    pages = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_toy_step_raw.csv")))
+    if not pages:
+        return None, None
+    page = pages[-1]
+    try:
+        rows = list(csv.reader(open(page)))
+        hdr, units, body = rows[0], rows[1], [r for r in rows[2:] if "toy_step_kernel" in r[hdr.index("Kernel Name")]]
+        scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+        total = 0.0
+        for name in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+            i = hdr.index(name)
+            total += sum(float(r[i]) for r in body) / len(body) * scale[units[i]]
+        return total, os.path.relpath(page, ROOT)
+    except Exception:
+        return None, os.path.relpath(page, ROOT)
+
+
+def golden_parity(c):
+    """Outside every timed region: the drop-in demo.py loop for 200 iterations from seed 1234 on THIS
+    world size, once per gradient route, against the reference's own run at the same world size
+    (tests/golden/ref_w{W}.npz, minted by tests/golden/make_golden.py from /root/reference/demo.py).
+    Tolerances are those of tests/test_gpu_multi.py: logged losses rel 2e-5, parameters abs 2e-5 after
+    200 steps, replicas bit-identical."""
+    import hashlib
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    import demo
+    from distributed_training_pytorch_b200 import DataLoader, DistributedSampler, ToyData, ToyModel
+    from distributed_training_pytorch_b200 import DistributedDataParallel as DDP
+
+    path = os.path.join(ROOT, "tests", "golden", f"ref_w{c.world}.npz")
+    if not os.path.exists(path):
+        return {"w": c.world, "ok": None, "skipped": f"no golden file for world {c.world}"}
+    g = np.load(path)
+    ref = np.stack([g["lossX"], g["lossY"]], axis=1)[:200]
+    routes = ["single"] if c.world == 1 else ["p2p", "nccl"]
+    out = {"w": c.world, "steps": 200, "golden": os.path.relpath(path, ROOT),
+           "tolerance": {"loss_rel": 2e-5, "param_abs": 2e-5, "replicas": "bit-identical"}}
+    saved = {k: os.environ.get(k) for k in ("DDPB_ALLREDUCE", "DDPB_ITERATIONS", "DDPB_NO_WANDB", "DDPB_FUSED_LOSS")}
+    ok_all = True
+    for route in routes:
+        os.environ.update(DDPB_ALLREDUCE="p2p" if route == "single" else route, DDPB_ITERATIONS="200", DDPB_NO_WANDB="1")
+        os.environ.pop("DDPB_FUSED_LOSS", None)
+        torch.manual_seed(1234)
+        mx, my = ToyModel(), ToyModel()
+        data = ToyData()
+        model_X, model_Y = DDP(mx.cuda(), device_ids=[c.local_rank]), DDP(my.cuda(), device_ids=[c.local_rank])
+        sampler = DistributedSampler(data, shuffle=True)
+        loader = DataLoader(data, batch_size=BATCH, shuffle=False, pin_memory=True, num_workers=0, sampler=sampler)
+        logged = []
+        demo.training_demo(model_X, model_Y, loader, sampler, c.world, on_loss=lambda it, lx, ly: logged.append((lx, ly)))
+        px, py = model_X.flat_parameters().cpu().numpy(), model_Y.flat_parameters().cpu().numpy()
+        digest = hashlib.sha256(px.tobytes() + py.tobytes()).hexdigest()
+        digests = [None] * c.world
+        dist.all_gather_object(digests, digest, group=c.side)
+        rec = {"fused_exchange": bool(model_X._backend.fused_exchange), "replicas_identical": len(set(digests)) == 1,
+               "params_sha256": digest[:16]}
+        if c.rank == 0:
+            losses = np.asarray(logged, np.float32)
+            rec["loss_rel_max"] = float(np.max(np.abs(losses - ref) / ref)) if losses.shape == ref.shape else None
+            rec["param_abs_max"] = float(max(np.max(np.abs(px - g["mid_X"])), np.max(np.abs(py - g["mid_Y"]))))
+            rec["ok"] = bool(rec["loss_rel_max"] is not None and rec["loss_rel_max"] <= 2e-5 and rec["param_abs_max"] <= 2e-5
+                             and rec["replicas_identical"] and (route != "p2p" or rec["fused_exchange"]))
+        flags = [rec.get("ok")]
+        dist.broadcast_object_list(flags, src=0, group=c.side)
+        rec["ok"] = flags[0]
+        ok_all = ok_all and bool(flags[0])
+        out[route] = rec
+        del model_X, model_Y
+    for k, v in saved.items():
+        if v is None:
+            os.environ.pop(k, None)
+        else:
+            os.environ[k] = v
+    out["ok"] = ok_all
+    return out
+
+
+def incumbent_torch(c, hidden, batch, steps, allow_tf32):
+    """The GPU incumbent: the reference's own stock-PyTorch modules (nn.Linear /
+    LeakyReLU / MSELoss / optim.Adam, torch DDP over NCCL when W > 1) on the SAME GPU, inputs resident.
+    Returns ms per iteration of one model's step (max over ranks)."""
+    import torch
+    import torch.nn as tnn
+    prev = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = bool(allow_tf32)
+    try:
+        torch.manual_seed(0)
+        dims = (2, hidden, hidden, hidden, hidden, 1)
+        layers = []
+        for i in range(5):
+            layers.append(tnn.Linear(dims[i], dims[i + 1]))
+            if i < 4:
+                layers.append(tnn.LeakyReLU())
+        model = tnn.Sequential(*layers).cuda()
+        if c.world > 1:
+            model = torch.nn.parallel.DistributedDataParallel(model, device_ids=[c.local_rank])
+        opt = torch.optim.Adam(model.parameters(), lr=1e-3)
+        loss_fn = tnn.MSELoss()
+        z = torch.randn(batch, device="cuda")
+        x, y = torch.stack([z, z], 1).contiguous(), (z * z).view(batch, 1).contiguous()
+
+        def step():
+            opt.zero_grad(set_to_none=True)
+            loss_fn(model(x), y).backward()
+            opt.step()
+        for _ in range(5):
+            step()
+        c.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            step()
+        e1.record()
+        c.barrier()
+        return c.max_over_ranks(e0.elapsed_time(e1)) / steps
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = prev
+
+
+def wide_record(c, peaks):
+    """BASELINE.json configs[4]: the widened toy model (hidden width 4096), local batch 256 on one GPU
+    and 512 / W on W GPUs (demo.py's 512-sample epoch), through the front end; per-kernel medians
+    (CUDA events, L2 flushed) on one GPU; the stock-PyTorch incumbent beside it."""
+    import torch
+
+    import distributed_training_pytorch_b200 as b200
+    from distributed_training_pytorch_b200 import _lib
+    H = int(os.environ.get("DDPB_BENCH_WIDE_HIDDEN", "4096"))
+    B = BATCH if c.world == 1 else max(1, DATASET // c.world)
+    steps = 30
+    torch.manual_seed(0)
+    model = b200.DistributedDataParallel(b200.ToyModel(hidden=H).cuda(), device_ids=[c.local_rank])
+    opt = b200.optim.Adam(model.parameters(), lr=1e-3)
+    loss_fn = b200.nn.MSELoss()
+    z = torch.randn(B, device="cuda")
+    x, y = torch.stack([z, z], 1).contiguous(), (z * z).view(B, 1).contiguous()
+
+    def step():
+        opt.zero_grad(set_to_none=True)
+        l = loss_fn(model(x), y)
+        l.backward()
+        opt.step()
+        return l
+    for _ in range(5):
+        step()
+    c.barrier()
+    t_begin = time.perf_counter()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        last = step()
+    e1.record()
+    c.barrier()
+    ms = c.max_over_ranks(e0.elapsed_time(e1)) / steps
+    final_loss = float(last.detach().cpu())
+    be = model._backend
+    P = be.P
+    hbm = peaks["hbm_gbs"]
+    rec = {"workload": f"widened ToyModel(hidden={H}), Adam lr=1e-3, local batch {B}, {c.world} GPU(s)", "hidden": H,
+           "params": P, "local_batch": B, "global_batch": B * c.world, "dtype": "tf32 multiply, fp32 accumulate/storage",
+           "steps": steps, "ms_per_step": ms, "value": B * c.world / (ms * 1e-3), "unit": UNIT,
+           "allreduce": ("none" if c.world == 1 else "fused peer-window reduce+Adam kernel per bucket" if be.fused_exchange
+                         else "ncclAllReduce + fused avg+Adam"),
+           "buckets": len(be.buckets), "loss_after": final_loss,
+           "floors_ms": {"hbm_40B_per_param": 40.0 * P / (hbm * 1e9) * 1e3,
+                         "nvlink_allreduce": (2.0 * (c.world - 1) / c.world * 4.0 * P / 900e9 * 1e3) if c.world > 1 else 0.0}}
+    if c.world == 1:
+        L = _lib.lib()
+        st = torch.cuda.current_stream().cuda_stream
+        w, bias = be._w(2)
+        gw, gb = be._g(2)
+
+        def timed(fn, reps=15):
+            ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(reps)]
+            for a, b in ev:
+                c.flush_buf.fill_(1)
+                a.record(); fn(); b.record()
+            torch.cuda.synchronize()
+            t = sorted(a.elapsed_time(b) for a, b in ev)
+            return t[len(t) // 2]
+        k = {"fwd": timed(lambda: L.ddpb_linear_fwd(be.act[0].data_ptr(), w, bias, be.act[1].data_ptr(), be.act_t[1].data_ptr(), B, H, H, be.ld, 1, st)),
+             "dgrad": timed(lambda: L.ddpb_linear_dgrad(be.dz[0].data_ptr(), w, be.act[0].data_ptr(), be.dz[1].data_ptr(), be.dz_t[1].data_ptr(), B, H, H, be.ld, st)),
+             "wgrad": timed(lambda: L.ddpb_linear_wgrad(be.dz_t[0].data_ptr(), be.act_t[0].data_ptr(), gw, gb, B, H, H, be.ld, st)),
+             "adam": timed(lambda: be._update(0, P, st, False))}
+        wbytes = 4.0 * H * H
+        rec["kernels"] = {
+            name: {"ms": k[name], "bound": "hbm", "algorithmic_bytes": wbytes, "achieved_gbs": wbytes / (k[name] * 1e-3) / 1e9,
+                   "frac": wbytes / (k[name] * 1e-3) / 1e9 / hbm, "tflops": 2.0 * B * H * H / (k[name] * 1e-3) / 1e12}
+            for name in ("fwd", "dgrad", "wgrad")}
+        rec["kernels"]["adam"] = {"ms": k["adam"], "bound": "hbm", "algorithmic_bytes": 28.0 * P,
+                                  "achieved_gbs": 28.0 * P / (k["adam"] * 1e-3) / 1e9, "frac": 28.0 * P / (k["adam"] * 1e-3) / 1e9 / hbm}
+        rec["kernels_note"] = ("median of CUDA-event pairs with a 256 MiB L2 flush before each launch (includes the "
+                               "launch gap); algorithmic bytes 4*H*H per GEMM (the weight stream), 28*P for Adam")
+    c.windows.append((t_begin, time.perf_counter()))
+    if hasattr(be, "close"):
+        be.close()
+    del model, opt, be
+    torch.cuda.empty_cache()
+    # the incumbent: stock PyTorch on the same GPU(s), same shapes
+    inc = {}
+    for name, tf32 in (("fp32", False), ("tf32", True)):
+        t_begin = time.perf_counter()
+        t = incumbent_torch(c, H, B, 20, tf32)
+        c.windows.append((t_begin, time.perf_counter()))
+        inc[name] = {"ms_per_step": t, "value": B * c.world / (t * 1e-3),
+                     "what": f"torch {torch.__version__} nn.Linear/LeakyReLU/MSELoss/optim.Adam"
+                             f"{' + torch DDP (NCCL)' if c.world > 1 else ''}, allow_tf32={tf32}"}
+    rec["incumbent_torch_gpu"] = inc
+    rec["speedup_vs_incumbent"] = {k: v["ms_per_step"] / ms for k, v in inc.items()}
+    torch.cuda.empty_cache()
+    return rec
+
+
+def pipeline_record(c):
+    """BASELINE.json configs[3]: MultiGPUModel split over two GPUs of one process (rank 0 only, GPUs 0/1;
+    needs W >= 2 so that a second GPU exists).  Step time through the front end, the latency split of
+    the three launches, and the stock-PyTorch incumbent (the reference's .to(dev1) version)."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        return None
+    c.barrier()
+    rec = None
+    if c.rank == 0:
+        import torch.nn as tnn
+
+        import distributed_training_pytorch_b200 as b200
+        d0, d1 = 0, 1
+        torch.manual_seed(1234)
+        # this record runs on rank 0 alone: a one-process pipeline, no collectives
+        model = b200.DistributedDataParallel(b200.MultiGPUModel(d0, d1), device_ids=None, process_group=b200.LOCAL_ONLY)
+        opt = b200.optim.Adam(model.parameters(), lr=1e-3)
+        loss_fn = b200.nn.MSELoss()
+        z = torch.randn(BATCH)
+        x = torch.stack([z, z], 1).contiguous().to(d0)
+        y = (z * z).view(BATCH, 1).contiguous().to(d1)
+
+        def step(read):
+            opt.zero_grad(set_to_none=True)
+            l = loss_fn(model(x), y)
+            l.backward()
+            opt.step()
+            return float(l.detach().cpu()) if read else None
+        for _ in range(20):
+            step(True)
+        steps = 300
+        for d in (d0, d1):
+            torch.cuda.synchronize(d)
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            step(True)
+        wall_read = (time.perf_counter() - t0) / steps * 1e3
+        with torch.cuda.device(d0):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            for d in (d0, d1):
+                torch.cuda.synchronize(d)
+            e0.record()
+            for _ in range(steps):
+                step(False)
+            e1.record()
+            for d in (d0, d1):
+                torch.cuda.synchronize(d)
+            dev_ms = e0.elapsed_time(e1) / steps
+        # latency split of one iteration: events around the three launches
+        be = model._backend
+        split = be.timed_split(x, y, 50) if hasattr(be, "timed_split") else None
+        # incumbent: the reference's model, verbatim structure (demo_one_model_multi_gpu.py:17-42)
+        torch.manual_seed(1234)
+        l0 = tnn.Sequential(tnn.Linear(2, 10), tnn.LeakyReLU(), tnn.Linear(10, 10), tnn.LeakyReLU()).to(d0)
+        l1 = tnn.Sequential(tnn.Linear(10, 10), tnn.LeakyReLU(), tnn.Linear(10, 10), tnn.LeakyReLU(), tnn.Linear(10, 1)).to(d1)
+        topt = torch.optim.Adam(list(l0.parameters()) + list(l1.parameters()), lr=1e-3)
+        tl = tnn.MSELoss()
+
+        def tstep():
+            topt.zero_grad(set_to_none=True)
+            loss = tl(l1(l0(x).to(d1)), y)
+            loss.backward()
+            topt.step()
+            return float(loss.detach().cpu())
+        for _ in range(20):
+            tstep()
+        t0 = time.perf_counter()
+        for _ in range(100):
+            tstep()
+        inc_ms = (time.perf_counter() - t0) / 100 * 1e3
+        rec = {"workload": "demo_one_model_multi_gpu.py: MultiGPUModel (2->10->10 | 10->10->10->1) on GPUs 0/1 of one process, "
+                           "B=256, Adam", "ms_per_step_device": dev_ms, "ms_per_step_with_loss_read": wall_read,
+               "value": BATCH / (wall_read * 1e-3), "unit": UNIT, "launches_per_step": 3, "latency_split_us": split,
+               "incumbent_torch_gpu": {"ms_per_step_with_loss_read": inc_ms, "value": BATCH / (inc_ms * 1e-3),
+                                       "what": f"torch {torch.__version__} modules with .to(dev1) between the stages, loss read every step"},
+               "speedup_vs_incumbent": inc_ms / wall_read,
+               "timing": "device: one CUDA-event pair on GPU 0 around 300 steps without loss reads; with_loss_read: host wall "
+                         "clock around 300 steps that read the loss every step (the reference's loop logs it every step)"}
+    # the other ranks wait on the HOST (gloo): an NCCL barrier would park a spinning kernel on GPU 1, which
+    # rank 0's second stage is using
+    import torch.distributed as dist
+    dist.barrier(group=c.side)
+    return rec
+
+
 def ours(args):
     import torch
     import torch.distributed as dist
@@ -181,7 +493,7 @@ def ours(args):
         dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{free_port()}", rank=0, world_size=1)
     side = dist.new_group(backend="gloo")
     eng = engine_for(local_rank)
-    K, W = args.steps, args.warmup
+    K, W = args.steps, max(args.warmup, 3)
     lb, gb = local_batch(world), global_batch(world)
 
     def barrier():
@@ -195,10 +507,24 @@ def ours(args):
         return float(t)
 
     flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")      # 2x the 126 MB L2
+    c = Ctx()
+    c.world, c.rank, c.local_rank, c.side, c.barrier, c.max_over_ranks, c.flush_buf = world, rank, local_rank, side, barrier, max_over_ranks, flush_buf
+    c.windows = windows = []
 
-    def build(device_resident):
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        peaks = json.load(open(peaks_path))
+        peak, peak_src = peaks["hbm_gbs"], "measured (MEASURED_PEAKS.json hbm_gbs, burst)"
+    else:
+        peaks = {"hbm_gbs": 6650.0}
+        peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+
+    # ---- parity first (outside every timed region): a bench line without it is not printed green
+    parity = None if args.no_parity else golden_parity(c)
+
+    def build(device_resident, n_data=DATASET):
         torch.manual_seed(1234)
-        mx, my, data = ToyModel(), ToyModel(), ToyData()
+        mx, my, data = ToyModel(), ToyModel(), ToyData(n_data)
         model_X, model_Y = DDP(mx.cuda(), device_ids=[local_rank]), DDP(my.cuda(), device_ids=[local_rank])
         sampler = DistributedSampler(data, shuffle=True)
         loader = DataLoader(data, batch_size=BATCH, shuffle=False, pin_memory=True, num_workers=0, sampler=sampler,
@@ -216,7 +542,9 @@ def ours(args):
 
     loss_fn = nn.MSELoss()
 
-    def one_step(models, opts, batch, read_loss):
+    def one_step(models, opts, batch, read):
+        """One iteration of demo.py's loop.  read: None (no loss read), "local" (loss.detach().cpu()),
+        "fused" (the all-rank mean out of the gradient exchange), "gloo" (the reference's two host collectives)."""
         data, target = batch
         for o in opts:
             o.zero_grad(set_to_none=True)
@@ -228,36 +556,50 @@ def ours(args):
             losses.append(l)
         for o in opts:
             o.step()
-        if read_loss:
+        if read is None:
+            eng.flush()
+            return None
+        if read == "local" or world == 1:
             return [l.detach().cpu() for l in losses]
-        eng.flush()
-        return None
+        if read == "fused":
+            return [l.detach().global_mean() for l in losses]
+        out = []
+        bs = target.size(0)
+        for l in losses:
+            t = l.detach().cpu() * bs
+            dist.all_reduce(t, group=side, op=dist.ReduceOp.SUM)
+            out.append(t / (bs * world))
+        return out
 
     clock = ClockSampler(local_rank)
     clock.start()
-    windows = []
 
-    # ---- value: HBM-resident inputs, per-step events, L2 flushed between timed steps
-    model_X, model_Y, sampler, loader, opts = build(device_resident=True)
-    batches = iteration_stream(sampler, loader)
-    for _ in range(max(W, 3)):
-        one_step((model_X, model_Y), opts, next(batches), read_loss=False)
-    barrier()
-    starts = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
-    stops = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
-    launches0 = eng.launches
-    t_begin = time.perf_counter()
-    for i in range(K):
-        flush_buf.fill_(i & 0xff)                     # evict L2 (outside the timed region)
-        batch = next(batches)
-        starts[i].record()
-        one_step((model_X, model_Y), opts, batch, read_loss=False)
-        stops[i].record()
-    barrier()
-    windows.append((t_begin, time.perf_counter()))
-    launches = eng.launches - launches0
-    cold_ms = sum(s.elapsed_time(e) for s, e in zip(starts, stops))
-    cold_ms = max_over_ranks(cold_ms)
+    def cold_leg(n_data, steps):
+        """HBM-resident inputs, per-step events, L2 flushed between timed steps."""
+        model_X, model_Y, sampler, loader, opts = build(True, n_data)
+        batches = iteration_stream(sampler, loader)
+        for _ in range(W):
+            one_step((model_X, model_Y), opts, next(batches), None)
+        barrier()
+        starts = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
+        stops = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
+        launches0 = eng.launches
+        t_begin = time.perf_counter()
+        for i in range(steps):
+            flush_buf.fill_(i & 0xff)                     # evict L2 (outside the timed region)
+            batch = next(batches)
+            starts[i].record()
+            one_step((model_X, model_Y), opts, batch, None)
+            stops[i].record()
+        barrier()
+        windows.append((t_begin, time.perf_counter()))
+        launches = eng.launches - launches0
+        ms = max_over_ranks(sum(s.elapsed_time(e) for s, e in zip(starts, stops)))
+        return ms, launches, (model_X, model_Y, sampler, loader, opts, batches)
+
+    # ---- value: strong scaling of demo.py's 512-sample epoch
+    cold_ms, launches, kept = cold_leg(DATASET, K)
+    model_X, model_Y, sampler, loader, opts, batches = kept
 
     # ---- hot_l2: same steps back to back, straight through the C ABI as ONE captured CUDA graph
     # of K fused launches (each node carries its sampler row; step counters live on the device),
@@ -266,24 +608,23 @@ def ours(args):
     direct = None
     fused = world == 1 or model_X._backend.fused_exchange
     if fused:
+        import ctypes
         eng.flush()
         n_rows = 1024
         per_epoch = len(sampler) // lb
         rows = torch.from_numpy(sampler.epochs_i32(0, n_rows // per_epoch).reshape(n_rows, lb)).cuda()
         jobs = (_lib.ToyJob * _lib.MAX_JOBS)()
         for i, m in enumerate((model_X, model_Y)):
-            j = m._backend.job
+            j = _lib.ToyJob.from_buffer_copy(m._backend.job)
             j.loss_ring = m._backend.loss_dev.data_ptr()          # nobody reads losses in this loop: keep them in HBM
+            j.global_loss_ring = None
             j.x, j.y, j.idx = loader._dev[0].data_ptr(), loader._dev[1].data_ptr(), rows.data_ptr()
             j.idx_rows, j.idx_stride, j.B, j.mode, j.n_data = n_rows, lb, lb, _lib.MODE_STEP, DATASET
             jobs[i] = j
         stream = torch.cuda.current_stream().cuda_stream
-        toy_step = _lib.lib().ddpb_toy_step
-
-        # capture K back-to-back steps once; the replay is what is timed
-        import ctypes
-        graph = ctypes.c_void_p()
         L = _lib.lib()
+        toy_step = L.ddpb_toy_step
+        graph = ctypes.c_void_p()
         side_stream = torch.cuda.Stream()
         with torch.cuda.stream(side_stream):
             cap = side_stream.cuda_stream
@@ -309,51 +650,91 @@ def ours(args):
         direct()                                      # one graph launch = K fused steps
     else:
         for i in range(K):
-            one_step((model_X, model_Y), opts, next(batches), read_loss=False)
+            one_step((model_X, model_Y), opts, next(batches), None)
     ev1.record()
     barrier()
     windows.append((t_begin, time.perf_counter()))
     hot_ms = max_over_ranks(ev0.elapsed_time(ev1))
+    del kept, model_X, model_Y, sampler, loader, opts, batches
 
-    # ---- e2e: pinned host batches through the public front end, loss read back every step
-    model_X, model_Y, sampler, loader, opts = build(device_resident=False)
-    batches = iteration_stream(sampler, loader)
-    for _ in range(max(W, 3)):
-        one_step((model_X, model_Y), opts, next(batches), read_loss=True)
-    barrier()
-    t_begin = time.perf_counter()
-    e2e_ms = 0.0
-    last = None
-    for i in range(K):
-        flush_buf.fill_(i & 0xff)
-        torch.cuda.synchronize()
-        ev0.record()
-        last = one_step((model_X, model_Y), opts, next(batches), read_loss=True)
-        ev1.record()
-        ev1.synchronize()
-        e2e_ms += ev0.elapsed_time(ev1)
-    barrier()
-    windows.append((t_begin, time.perf_counter()))
-    e2e_ms = max_over_ranks(e2e_ms)
+    # ---- weak scaling (secondary): the dataset grows with W (256 * W samples), so every rank
+    # keeps B = 256 and the exchange is the only thing that changes with W
+    weak = None
+    if world > 1:
+        Kw = min(K, 500)
+        weak_ms, _, kept = cold_leg(BATCH * world, Kw)
+        weak = {"value": Kw * BATCH * world / (weak_ms * 1e-3), "unit": UNIT, "ms_per_step": weak_ms / Kw, "steps": Kw,
+                "dataset": BATCH * world, "local_batch": BATCH, "global_batch": BATCH * world, "scaling": "weak",
+                "timing": "as `value`: CUDA events per step, L2 flushed, max over ranks"}
+        del kept
+
+    # ---- e2e: pinned host batches through the public front end, the step's loss read back every step.
+    # W > 1: the loss that is read is the one demo.py logs, the mean over all ranks -- by default out of
+    # the gradient exchange (bucket element 371), and as `e2e_gloo_loss` the reference's way (local
+    # loss.cpu() + two gloo all-reduces per step, demo.py:112-121).
+    def e2e_leg(read, steps):
+        model_X, model_Y, sampler, loader, opts = build(False)
+        batches = iteration_stream(sampler, loader)
+        for _ in range(W):
+            one_step((model_X, model_Y), opts, next(batches), read)
+        barrier()
+        t_begin = time.perf_counter()
+        total, wall, last = 0.0, 0.0, None
+        for i in range(steps):
+            flush_buf.fill_(i & 0xff)
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            ev0.record()
+            last = one_step((model_X, model_Y), opts, next(batches), read)
+            ev1.record()
+            ev1.synchronize()
+            wall += time.perf_counter() - t0
+            total += ev0.elapsed_time(ev1)
+        barrier()
+        windows.append((t_begin, time.perf_counter()))
+        return max_over_ranks(total), max_over_ranks(wall * 1e3), last, (model_X, model_Y, opts, batches)
+
+    read_mode = "local" if world == 1 else ("gloo" if os.environ.get("DDPB_FUSED_LOSS", "1") == "0" else "fused")
+    e2e_ms, e2e_wall_ms, last, kept = e2e_leg(read_mode, K)
+    e2e_gloo = None
+    if world > 1 and read_mode == "fused":
+        Kg = min(K, 300)
+        g_ms, _, _, kept2 = e2e_leg("gloo", Kg)
+        e2e_gloo = {"value": Kg * gb / (g_ms * 1e-3), "unit": UNIT, "ms_per_step": g_ms / Kg, "steps": Kg,
+                    "loss_reduction": "loss.detach().cpu() * B + 2 gloo all_reduce per step (reference demo.py:112-121)"}
+        del kept2
 
     # keep the GPU busy long enough for nvidia-smi to see the clocks this workload runs at
+    model_X, model_Y, opts, batches = kept
     t_begin = time.perf_counter()
     while time.perf_counter() - t_begin < 1.0:
         for _ in range(200):
-            one_step((model_X, model_Y), opts, next(batches), read_loss=False)
+            one_step((model_X, model_Y), opts, next(batches), None)
         torch.cuda.synchronize()
     windows.append((t_begin, time.perf_counter()))
+    del kept, model_X, model_Y, opts, batches
+
+    # ---- secondary configurations (extra keys; same clock sampler)
+    wide = None if args.no_wide else wide_record(c, peaks)
+    pipeline = None if (args.no_pipeline or world < 2) else pipeline_record(c)
+    barrier()
+    incumbent = None
+    if not args.no_incumbent:
+        t_begin = time.perf_counter()
+        t = incumbent_torch(c, H, lb, 100, False)
+        windows.append((t_begin, time.perf_counter()))
+        incumbent = {"ms_per_step": 2 * t, "value": gb / (2 * t * 1e-3), "unit": UNIT,
+                     "what": f"torch {torch.__version__} eager: 2 x (nn.Linear/LeakyReLU MLP, MSELoss, backward, optim.Adam)"
+                             f"{' under torch DDP (NCCL)' if world > 1 else ''}, resident inputs, no loss read; one model "
+                             "timed, doubled for demo.py's two", "compare_with": "hot_l2 / value (resident inputs)"}
     clocks = clock.stop(windows)
 
-    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
-    if os.path.exists(peaks_path):
-        peak, peak_src = json.load(open(peaks_path))["hbm_gbs"], "measured (MEASURED_PEAKS.json hbm_gbs, burst)"
-    else:
-        peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
     # algorithmic bytes per launch: per model 4P (bucket) + 28P (Adam) + 48*B*H + 8*B (activations)
     alg_bytes = 2 * (4 * P + 28 * P + 48 * lb * H + 8 * lb)
-    kernel_ms = hot_ms / K if fused else None
-    achieved = alg_bytes / (kernel_ms * 1e-3) / 1e9 if kernel_ms else None
+    kernel_ms = cold_ms / K                             # the same timing `value` is computed from
+    achieved = alg_bytes / (kernel_ms * 1e-3) / 1e9
+    hot_kernel_ms = hot_ms / K if fused else None
+    traffic, traffic_src = ncu_traffic() if lb == BATCH else (None, None)
 
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -364,36 +745,57 @@ def ours(args):
                                   "stock torch CPU path (oracle/torch_ref.py, bit-identical to the reference run)"}
 
     if rank == 0:
+        be_fused = world > 1 and fused
         line = {"metric": METRIC, "value": K * gb / (cold_ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": K,
-                "warmup": max(W, 3), "ms_per_step": cold_ms / K, "higher_is_better": True, "scaling": "strong",
+                "warmup": W, "ms_per_step": cold_ms / K, "higher_is_better": True, "scaling": "strong",
                 "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                "config": dict(workload(world), timing="CUDA events per step; L2 flushed (256 MiB fill) between timed "
-                                                       "steps; max over ranks",
-                               parallelism=f"dp{world}",
-                               allreduce=("none (single rank)" if world == 1 else
-                                          "fused one-shot exchange over NVLink peer windows inside the step kernel"
-                                          if model_X._backend.fused_exchange else "ncclAllReduce per bucket + fused avg+Adam"),
-                               scaling_note="one 512-sample epoch is the fixed job: 2 steps at W=1, 1 step at W>=2"),
+                "config": workload(world),
+                "notes": {"timing": "CUDA events per step; L2 flushed (256 MiB fill) between timed steps; max over ranks",
+                          "parallelism": f"dp{world}",
+                          "allreduce": ("none (single rank)" if world == 1 else
+                                        "fused one-shot exchange over NVLink peer windows inside the step kernel"
+                                        if be_fused else "ncclAllReduce per bucket + fused avg+Adam"),
+                          "scaling_note": "one 512-sample epoch is the fixed job: 2 steps at W=1, 1 step at W>=2"},
                 "hot_l2": {"value": K * gb / (hot_ms * 1e-3), "unit": UNIT, "ms_per_step": hot_ms / K,
                            "timing": "one CUDA-event pair around K back-to-back steps, no flush"
                                      + ("; the K launches are one captured CUDA graph" if fused else "")},
                 "e2e": {"value": K * gb / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms / K,
-                        "h2d_bytes_per_step": lb * 12, "d2h_bytes_per_step": 8},
+                        "host_wall_ms_per_step": e2e_wall_ms / K,
+                        "h2d_bytes_per_step": lb * 12, "d2h_bytes_per_step": 8 if read_mode == "local" else 16,
+                        "h2d": "the step kernel loads the batch (x | y rows) from the loader's pinned staging block over "
+                               "PCIe (mapped host memory); no copy-engine operation",
+                        "d2h": "the kernel stores each model's loss into a pinned ring the host polls",
+                        "loss_read": {"local": "loss.detach().cpu() of both models, every step",
+                                      "fused": "loss.detach().global_mean() of both models, every step: the all-rank mean "
+                                               "out of the gradient exchange (no host collective)",
+                                      "gloo": "loss.detach().cpu() + 2 gloo all_reduce, every step"}[read_mode]},
+                "e2e_gloo_loss": e2e_gloo,
+                "weak": weak,
                 "gpu_launches": launches,
                 "clocks": clocks,
-                "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                             "frac": (achieved / peak) if achieved else None,
-                             # dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu --set full,
-                             # profiles/r01_v3_toy_step_raw.csv (cold caches; warm launches hit L2)
-                             "traffic": 50432 if lb == BATCH else None,
+                "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                             "traffic": traffic,
+                             "traffic_source": (f"{traffic_src}: dram__bytes_read.sum + dram__bytes_write.sum per launch, "
+                                                "ncu --set full (cold caches)") if traffic_src else None,
                              "kernel": "toy_step_kernel", "peak_source": peak_src,
                              "algorithmic_bytes_per_launch": alg_bytes,
+                             "launch_ms": kernel_ms, "launch_ms_source": "the per-step CUDA events `value` is computed from "
+                                                                         "(cold L2, one launch per step)",
+                             "hot": ({"launch_ms": hot_kernel_ms, "achieved": alg_bytes / (hot_kernel_ms * 1e-3) / 1e9,
+                                      "frac": alg_bytes / (hot_kernel_ms * 1e-3) / 1e9 / peak,
+                                      "source": "K steps replayed as one CUDA graph, warm L2"} if hot_kernel_ms else None),
                              "note": "latency-bound by construction: 2 clusters x 8 CTAs, 273 KB and 1 MFLOP per launch"},
                 "cpu_baseline": cpu_baseline,
+                "parity": parity,
+                "incumbent_torch_gpu": incumbent,
+                "wide": wide,
+                "pipeline": pipeline,
                 "loss_after_bench": [float(v) for v in last] if last else None}
         emit(line)
     eng.destroy_comm()
     dist.destroy_process_group()
+    if parity is not None and parity.get("ok") is False:
+        raise SystemExit("golden parity check FAILED (see the `parity` record)")
 
 
 _RESULT_FD = None
@@ -421,6 +823,10 @@ def main():
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--no-cpu-baseline", dest="no_cpu_baseline", action="store_true")
+    ap.add_argument("--no-parity", dest="no_parity", action="store_true", help="skip the golden-fixture check")
+    ap.add_argument("--no-wide", dest="no_wide", action="store_true", help="skip the widened-model record")
+    ap.add_argument("--no-pipeline", dest="no_pipeline", action="store_true", help="skip the model-parallel record")
+    ap.add_argument("--no-incumbent", dest="no_incumbent", action="store_true", help="skip the stock-PyTorch GPU records")
     args = ap.parse_args()
     if args.impl == "reference":
         reference_arm(args)

@@ -8,7 +8,9 @@ as sm_100a kernels.
 
 Additive knobs (environment, so argument_parser stays verbatim): DDPB_ITERATIONS (default
 1000, demo.py:88), DDPB_SEED (seed torch before building models/data; the reference never
-applies --seed), DDPB_DEVICE_DATA=1 (HBM-resident dataset), DDPB_NO_WANDB=1.
+applies --seed), DDPB_DEVICE_DATA=1 (HBM-resident dataset), DDPB_NO_WANDB=1, DDPB_FUSED_LOSS=1 (the logged
+mean loss comes out of the gradient exchange instead of two gloo all-reduces per step, logged one
+iteration late), DDPB_SHARE_GPUS=1 (more ranks than GPUs; gloo backend).
 """
 import os
 
@@ -37,9 +39,9 @@ def setup_distributed(config):
     else:
         layout = bootstrap.init_slurm_env(config.backend, config.use_node_rank)
     bootstrap.announce(layout, config)
-    torch.cuda.set_device(layout.local_rank)              # process -> GPU binding (demo.py:66)
-    model_X = DDP(model_X.cuda(), device_ids=[layout.local_rank])
-    model_Y = DDP(model_Y.cuda(), device_ids=[layout.local_rank])
+    torch.cuda.set_device(layout.device)              # process -> GPU binding (demo.py:66)
+    model_X = DDP(model_X.cuda(), device_ids=[layout.device])
+    model_Y = DDP(model_Y.cuda(), device_ids=[layout.device])
     return model_X, model_Y, layout.world_size
 
 
@@ -55,6 +57,18 @@ def training_demo(model_X, model_Y, dataloader, sampler, world_size, on_loss=Non
     max_iterations = int(os.environ.get("DDPB_ITERATIONS", 1000))
     iteration, epoch, training = 0, 0, True
     iteration_pbar = tqdm(range(max_iterations), desc="Iteration", disable=rank != 0)
+    # DDPB_FUSED_LOSS=1 (additive knob): log from the loss that rides in the gradient bucket (see below)
+    fused_loss, behind = os.environ.get("DDPB_FUSED_LOSS") == "1", None
+
+    def log(it, mean_X, mean_Y):
+        if rank != 0:
+            return
+        if wandb is not None:
+            wandb.log({"loss/lossX": mean_X}, commit=False)
+            wandb.log({"loss/lossY": mean_Y})
+        if on_loss is not None:
+            on_loss(it, float(mean_X), float(mean_Y))
+
     while training:
         if sampler is not None:
             sampler.set_epoch(epoch)
@@ -71,26 +85,31 @@ def training_demo(model_X, model_Y, dataloader, sampler, world_size, on_loss=Non
             l_Y.backward()
             optimizer_X.step()
             optimizer_Y.step()
-            # logged value: sum_r(loss_r * B) / (B * W); assumes equal batch on every rank
             batch_size = target.size(0)
-            all_reduce_loss_X = l_X.detach().cpu() * batch_size
-            dist.all_reduce(all_reduce_loss_X, group=all_reduce_group, op=dist.ReduceOp.SUM)
-            all_reduce_loss_Y = l_Y.detach().cpu() * batch_size
-            dist.all_reduce(all_reduce_loss_Y, group=all_reduce_group, op=dist.ReduceOp.SUM)
-            if rank == 0:
-                mean_X = all_reduce_loss_X / (batch_size * world_size)
-                mean_Y = all_reduce_loss_Y / (batch_size * world_size)
-                if wandb is not None:
-                    wandb.log({"loss/lossX": mean_X}, commit=False)
-                    wandb.log({"loss/lossY": mean_Y})
-                if on_loss is not None:
-                    on_loss(iteration, float(mean_X), float(mean_Y))
+            if fused_loss:
+                # The same logged value, sum_r(loss_r * B) / (B * W), without the two blocking host
+                # collectives: the squared-error sum is element 371 of the gradient bucket, so the gradient
+                # exchange has already reduced it.  It is read ONE ITERATION LATE (when it has long
+                # arrived in pinned memory), so the host never waits for the GPU here.
+                if behind is not None:
+                    log(behind[0], behind[1].detach().global_mean(), behind[2].detach().global_mean())
+                behind = (iteration, l_X, l_Y)
+            else:
+                # logged value: sum_r(loss_r * B) / (B * W); assumes equal batch on every rank
+                all_reduce_loss_X = l_X.detach().cpu() * batch_size
+                dist.all_reduce(all_reduce_loss_X, group=all_reduce_group, op=dist.ReduceOp.SUM)
+                all_reduce_loss_Y = l_Y.detach().cpu() * batch_size
+                dist.all_reduce(all_reduce_loss_Y, group=all_reduce_group, op=dist.ReduceOp.SUM)
+                if rank == 0:
+                    log(iteration, all_reduce_loss_X / (batch_size * world_size), all_reduce_loss_Y / (batch_size * world_size))
             iteration_pbar.update(1)
             iteration += 1
             if iteration == max_iterations:
                 training = False
                 break
         epoch += 1
+    if behind is not None:
+        log(behind[0], behind[1].detach().global_mean(), behind[2].detach().global_mean())
     dist.destroy_process_group(all_reduce_group)
     if rank == 0:
         iteration_pbar.close()

@@ -31,9 +31,9 @@ def setup_distributed(config):
     model_X, model_Y = ToyModel(), ToyModel()
     layout = bootstrap.init_mpi(config.backend)
     bootstrap.announce(layout, config)
-    torch.cuda.set_device(layout.local_rank)
-    model_X = DDP(model_X.cuda(), device_ids=[layout.local_rank])
-    model_Y = DDP(model_Y.cuda(), device_ids=[layout.local_rank])
+    torch.cuda.set_device(layout.device)
+    model_X = DDP(model_X.cuda(), device_ids=[layout.device])
+    model_Y = DDP(model_Y.cuda(), device_ids=[layout.device])
     return model_X, model_Y
 
 

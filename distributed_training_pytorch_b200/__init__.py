@@ -13,7 +13,7 @@ from . import _lib
 from ._lib import DdpB200Error
 from .argument_parser import get_args
 from .data import DataLoader, DistributedSampler
-from .ddp import DistributedDataParallel
+from .ddp import LOCAL_ONLY, DistributedDataParallel
 from .loss import MSELoss
 from .optim import SGD, Adam
 from .toy_model_and_data import MultiGPUModel, ToyData, ToyModel
@@ -23,4 +23,4 @@ nn = SimpleNamespace(MSELoss=MSELoss)
 optim = SimpleNamespace(Adam=Adam, SGD=SGD)
 
 __all__ = ["DistributedDataParallel", "DataLoader", "DistributedSampler", "MSELoss", "Adam", "SGD", "nn", "optim",
-           "ToyModel", "ToyData", "MultiGPUModel", "get_args", "DdpB200Error"]
+           "ToyModel", "ToyData", "MultiGPUModel", "get_args", "DdpB200Error", "LOCAL_ONLY"]

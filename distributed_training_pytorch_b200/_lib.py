@@ -20,6 +20,8 @@ XCHG_WINDOW_BYTES = 2 * MAX_PEERS * XCHG_ROW * 8
 BUCKET_MAX = 1024
 BUCKET_FLAGS_BYTES = 2 * BUCKET_MAX * MAX_PEERS * 4 + BUCKET_MAX * 4
 TOY_HIDDEN, TOY_PARAMS = 10, 371
+LOSS_SENTINEL = 0x7FC0DEAD          # a NaN payload no kernel produces: "slot not written yet"
+LOSS_TIMEOUT_BITS = 0x7FC0DEAE      # DDPB_LOSS_TIMEOUT_BITS: the step gave up waiting for a peer
 
 
 class DdpB200Error(RuntimeError):
@@ -33,13 +35,21 @@ class OptState(ctypes.Structure):
 class ToyJob(ctypes.Structure):
     _fields_ = [("params", c_void_p), ("grads", c_void_p), ("m", c_void_p), ("v", c_void_p),
                 ("state", c_void_p), ("bias_table", c_void_p), ("loss_ring", c_void_p), ("x", c_void_p), ("y", c_void_p),
-                ("idx", c_void_p), ("out", c_void_p),
+                ("idx", c_void_p), ("out", c_void_p), ("global_loss_ring", c_void_p),
                 ("B", c_int32), ("mode", c_int32), ("opt", c_int32), ("loss_ring_n", c_int32),
                 ("idx_rows", c_int32), ("idx_stride", c_int32), ("bias_table_n", c_int32), ("n_data", c_int32),
                 ("lr", c_double), ("beta1", c_double), ("beta2", c_double), ("eps", c_double),
                 ("momentum", c_double),
                 ("peer_data", c_void_p * 8), ("peer_flags", c_void_p * 8),
                 ("world", c_int32), ("rank", c_int32), ("inv_world", c_float), ("reserved2", c_int32)]
+
+
+class ToyIter(ctypes.Structure):          # ddpb_toy_iter: one host call per iteration (gather, launch, loss wait)
+    _fields_ = [("jobs", c_void_p), ("stream", c_void_p), ("X", c_void_p), ("Y", c_void_p), ("idx", c_void_p),
+                ("out_x", c_void_p), ("out_y", c_void_p), ("wait_slot", c_void_p * (2 * MAX_JOBS)),
+                ("B", c_int64), ("spin_ns", c_int64),
+                ("njobs", c_int32), ("dx", c_int32), ("dy", c_int32), ("nwait", c_int32),
+                ("sentinel_bits", ctypes.c_uint32), ("wait_value", c_float * (2 * MAX_JOBS)), ("reserved", c_int32)]
 
 
 class SegJob(ctypes.Structure):
@@ -64,6 +74,7 @@ _SIGNATURES = {
     "ddpb_version": (c_int, []),
     "ddpb_last_error": (c_char_p, []),
     "ddpb_device_info": (c_int, [c_int, c_void_p, c_void_p, c_void_p]),
+    "ddpb_launch_count": (ctypes.c_longlong, []),
     "ddpb_randperm": (c_int, [c_uint64, c_int64, c_void_p]),
     "ddpb_sampler_indices": (c_int64, [c_int64, c_int, c_int, c_int, c_uint64, c_uint64, c_int, c_void_p, c_int64]),
     "ddpb_sampler_epochs_i32": (c_int, [c_int64, c_int, c_int, c_int, c_uint64, c_uint64, c_int, c_int, c_void_p, c_int64]),
@@ -73,6 +84,7 @@ _SIGNATURES = {
     "ddpb_toy_step": (c_int, [c_void_p, c_int, c_void_p]),
     "ddpb_toy_step_h2d": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_int64, c_void_p]),
     "ddpb_toy_step_virtual_ranks": (c_int, [c_void_p, c_int, c_void_p]),
+    "ddpb_toy_iteration": (c_int, [c_void_p]),
     "ddpb_linear_fwd": (c_int, [c_void_p] * 5 + [c_int] * 5 + [c_void_p]),
     "ddpb_linear_dgrad": (c_int, [c_void_p] * 5 + [c_int] * 4 + [c_void_p]),
     "ddpb_linear_wgrad": (c_int, [c_void_p] * 4 + [c_int] * 4 + [c_void_p]),
@@ -87,6 +99,8 @@ _SIGNATURES = {
     "ddpb_fused_avg_adam_dev": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_float,
                                         c_double, c_double, c_double, c_void_p, c_int, c_void_p, c_int, c_void_p]),
     "ddpb_fused_avg_sgd": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_float, c_double, c_double, c_int64, c_void_p]),
+    "ddpb_fused_avg_sgd_dev": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_float, c_double, c_double, c_void_p, c_int,
+                                       c_void_p]),
     "ddpb_bucket_reduce_adam": (c_int, [c_void_p, c_void_p]),
     "ddpb_nccl_load": (c_int, [c_char_p]),
     "ddpb_get_unique_id": (c_int, [c_void_p]),

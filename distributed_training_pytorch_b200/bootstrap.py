@@ -28,6 +28,15 @@ class Layout:
     local_rank: int
     local_world_size: int
 
+    @property
+    def device(self):
+        """CUDA device of this process: its local rank (demo.py:66).  DDPB_SHARE_GPUS=1 (additive knob)
+        wraps the local ranks around the visible GPUs, so that W processes can run on fewer than W GPUs
+        (gloo backend; used to exercise the W-rank gradient exchange on a one-GPU box)."""
+        if os.environ.get("DDPB_SHARE_GPUS") == "1":
+            return self.local_rank % max(1, torch.cuda.device_count())
+        return self.local_rank
+
 
 def _required_int(name):
     value = os.getenv(name, None)

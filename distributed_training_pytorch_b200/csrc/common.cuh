@@ -11,11 +11,17 @@ namespace ddpb {
 
 char *error_buffer();                                  // 512 bytes, thread-local
 int fail(int code, const char *fmt, ...);              // records text, returns code
+// Poll a pinned host word until it no longer holds `sentinel_bits` (util.cu, ddpb_wait_f32).
+int wait_slot(const float *host_slot, unsigned sentinel_bits, long long spin_ns, cudaStream_t stream, float *out);
 
 inline int cuda_fail(cudaError_t e, const char *what, const char *file, int line) {
     return fail(1000 + (int)e, "%s failed: %s (%s) at %s:%d", what, cudaGetErrorName(e),
                 cudaGetErrorString(e), file, line);
 }
+
+// Every kernel launch of the library is counted here (ddpb_launch_count): the number bench.py
+// reports as gpu_launches is read from this counter, not kept by the caller.
+void count_launch();
 
 }  // namespace ddpb
 

@@ -30,6 +30,7 @@ DDPB_API int ddpb_gather_batch(const float *X, const float *Y, const int32_t *id
     int blocks = (int)((total + 255) / 256);
     if (blocks > 148 * 8) blocks = 148 * 8;
     gather_rows_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(X, Y, idx, B, dx, dy, outX, outY);
+    ddpb::count_launch();
     DDPB_CUDA(cudaGetLastError());
     return 0;
 }

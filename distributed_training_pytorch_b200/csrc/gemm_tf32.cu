@@ -482,6 +482,7 @@ int launch(const Maps &mp, const EpiParams &ep, int M, int N, int K, cudaStream_
     cfg.attrs = &attr;
     cfg.numAttrs = 1;
     DDPB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tf32_kernel<EPI, B_MN, BN, SPLIT>, mp.a, mp.b, mp.o, mp.t, mp.c, ep, M, N, K));
+    ddpb::count_launch();
     return 0;
 }
 

@@ -94,7 +94,8 @@ __global__ void advance_state_kernel(ddpb_opt_state *state) { state->step += 1; 
 
 __global__ void __launch_bounds__(256)
 avg_sgd_kernel(const float *__restrict__ bucket, float *__restrict__ p, float *__restrict__ buf, long long n,
-               float grad_scale, float lr, float momentum, int first_step) {
+               float grad_scale, float lr, float momentum, int first_step, const ddpb_opt_state *state) {
+    if (state) first_step = state->step == 0;
     const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     const long long nthreads = (long long)gridDim.x * blockDim.x;
     for (long long i = tid; i < n; i += nthreads) {
@@ -288,6 +289,7 @@ DDPB_API int ddpb_fused_avg_adam(const float *bucket, float *p, float *m, float 
     avg_adam_kernel<<<stream_grid(n, 4), 256, 0, (cudaStream_t)stream>>>(
         bucket, p, m, v, n, grad_scale, lr, beta1, beta2, eps, std::pow(beta1, (double)step),
         std::pow(beta2, (double)step), nullptr, nullptr, 0);
+    ddpb::count_launch();
     DDPB_CUDA(cudaGetLastError());
     return 0;
 }
@@ -297,11 +299,16 @@ DDPB_API int ddpb_fused_avg_adam_dev(const float *bucket, float *p, float *m, fl
                                      int bias_table_n, ddpb_opt_state *state, int advance, void *stream) {
     DDPB_REQUIRE(bucket && p && m && v && n >= 0 && state && bias_table && bias_table_n >= 1,
                  "ddpb_fused_avg_adam_dev: bad arguments");
-    if (n > 0)
+    if (n > 0) {
         avg_adam_kernel<<<stream_grid(n, 4), 256, 0, (cudaStream_t)stream>>>(
             bucket, p, m, v, n, grad_scale, 0.0, beta1, beta2, eps, 0.0, 0.0, state,
             reinterpret_cast<const float2 *>(bias_table), bias_table_n);
-    if (advance) advance_state_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(state);
+        ddpb::count_launch();
+    }
+    if (advance) {
+        advance_state_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(state);
+        ddpb::count_launch();
+    }
     DDPB_CUDA(cudaGetLastError());
     return 0;
 }
@@ -311,7 +318,24 @@ DDPB_API int ddpb_fused_avg_sgd(const float *bucket, float *p, float *buf, int64
     DDPB_REQUIRE(bucket && p && n >= 0 && step >= 1 && (momentum == 0.0 || buf), "ddpb_fused_avg_sgd: bad arguments");
     if (n == 0) return 0;
     avg_sgd_kernel<<<stream_grid(n, 1), 256, 0, (cudaStream_t)stream>>>(bucket, p, buf, n, grad_scale, (float)lr,
-                                                                         (float)momentum, step == 1);
+                                                                         (float)momentum, step == 1, nullptr);
+    ddpb::count_launch();
+    DDPB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+DDPB_API int ddpb_fused_avg_sgd_dev(const float *bucket, float *p, float *buf, int64_t n, float grad_scale, double lr,
+                                    double momentum, ddpb_opt_state *state, int advance, void *stream) {
+    DDPB_REQUIRE(bucket && p && n >= 0 && state && (momentum == 0.0 || buf), "ddpb_fused_avg_sgd_dev: bad arguments");
+    if (n > 0) {
+        avg_sgd_kernel<<<stream_grid(n, 1), 256, 0, (cudaStream_t)stream>>>(bucket, p, buf, n, grad_scale, (float)lr,
+                                                                             (float)momentum, 0, state);
+        ddpb::count_launch();
+    }
+    if (advance) {
+        advance_state_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(state);
+        ddpb::count_launch();
+    }
     DDPB_CUDA(cudaGetLastError());
     return 0;
 }
@@ -324,6 +348,7 @@ int launch_bucket(const ddpb_bucket_job &job, cudaStream_t stream) {
     const int cap = (job.reserved >> 8) & 0xffff;            // diagnostic: cap the grid
     if (cap && grid > cap) grid = cap;
     bucket_reduce_adam_kernel<W><<<grid, 256, 0, stream>>>(job);
+    ddpb::count_launch();
     DDPB_CUDA(cudaGetLastError());
     return 0;
 }
@@ -358,6 +383,7 @@ DDPB_API int ddpb_bucket_reduce_adam(const ddpb_bucket_job *job, void *stream) {
     }
     if (job->advance) {
         advance_state_kernel<<<1, 1, 0, s>>>(job->state);
+        ddpb::count_launch();
         DDPB_CUDA(cudaGetLastError());
     }
     return 0;

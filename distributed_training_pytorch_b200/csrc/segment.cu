@@ -264,6 +264,7 @@ DDPB_API int ddpb_segment_step(const ddpb_seg_job *job, void *stream) {
         configured[dev] = true;
     }
     segment_kernel<<<1, kThreads, sizeof(SegSmem), (cudaStream_t)stream>>>(q);
+    ddpb::count_launch();
     DDPB_CUDA(cudaGetLastError());
     return 0;
 }

@@ -35,6 +35,7 @@
 // given identical gradients; only the batch-sum order of the gradients differs.
 #include "common.cuh"
 #include <cooperative_groups.h>
+#include <atomic>
 #include <cstddef>
 
 namespace cg = cooperative_groups;
@@ -134,6 +135,14 @@ __device__ __forceinline__ uint2 ld_slot_sys(const uint2 *p) {
     asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p) : "memory");
     return v;
 }
+
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+constexpr unsigned long long kPeerTimeoutNs = 2000000000ull;   // a peer that has not delivered after 2 s is gone
+constexpr unsigned kTimeoutSentinel = DDPB_LOSS_TIMEOUT_BITS;  // what the loss slot holds after a time-out
 
 __device__ __forceinline__ unsigned smem_addr(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
 
@@ -370,6 +379,7 @@ toy_step_kernel(const __grid_constant__ JobList jl) {
         const int opt = job.opt;
         float *const g_out = job.grads, *const p_out = job.params, *const m_out = job.m, *const v_out = job.v;
         float *const loss_slot = job.loss_ring ? job.loss_ring + wrap_index(seq, job.loss_ring_n) : nullptr;
+        float *const gloss_slot = job.global_loss_ring ? job.global_loss_ring + wrap_index(seq, job.loss_ring_n) : nullptr;
         const float inv_B = __fdiv_rn(1.0f, (float)B);
         mbar_wait(&S.mbar, 0);                            // all eight CTAs have pushed their partials
         DDPB_STAMP(3);
@@ -381,6 +391,7 @@ toy_step_kernel(const __grid_constant__ JobList jl) {
             if (own == P && loss_slot)                                       // local mean loss (what loss.cpu() returns)
                 *loss_slot = (B & (B - 1)) == 0 ? total * inv_B : __fdiv_rn(total, (float)B);
         }
+        bool timed_out = false;
         if (job.world > 1 && mode == DDPB_MODE_STEP) {
             // ---- one-shot all-reduce over NVLink, fused into the step (no NCCL launch, no second
             // kernel): slice c of every rank's bucket meets in every rank's receive window.
@@ -397,23 +408,46 @@ toy_step_kernel(const __grid_constant__ JobList jl) {
                 const size_t at = (size_t)(par * DDPB_MAX_PEERS + me) * kXchgRow + own;
                 for (int dst = 0; dst < W; ++dst)
                     st_slot_sys(reinterpret_cast<uint2 *>(jref.peer_data[dst]) + at, make_uint2(__float_as_uint(contrib), xseq));
-                total = 0.f;
                 const uint2 *mine = reinterpret_cast<const uint2 *>(jref.peer_data[me]) + (size_t)(par * DDPB_MAX_PEERS) * kXchgRow + own;
-                for (int src = 0; src < W; ++src) {
-                    uint2 got = ld_slot_sys(mine + (size_t)src * kXchgRow);
-                    long long spins = 0;
-                    while (got.y != xseq) {
-                        if (++spins > (1ll << 26)) {                         // ~1 s: a peer died; fail loudly, do not hang
-                            job.state->reserved[0] = 1;
-                            break;
-                        }
-                        got = ld_slot_sys(mine + (size_t)src * kXchgRow);
+                // All W slots are polled together: the loads of one round are in flight at the same
+                // time (one NVLink/L2 round trip per round, not W).  The wait is bounded by the global
+                // timer (kPeerTimeoutNs): a peer that never delivers makes this rank give up LOUDLY --
+                // state->reserved[0] is set, the loss slot gets the time-out sentinel, and neither the
+                // parameters, the moments nor the counters are touched, so the state stays the one of
+                // the last completed step.
+                uint2 got[DDPB_MAX_PEERS];
+                unsigned long long t0 = 0;
+                unsigned rounds = 0;
+                for (;;) {
+                    bool all = true;
+#pragma unroll
+                    for (int src = 0; src < DDPB_MAX_PEERS; ++src)
+                        if (src < W) got[src] = ld_slot_sys(mine + (size_t)src * kXchgRow);
+#pragma unroll
+                    for (int src = 0; src < DDPB_MAX_PEERS; ++src)
+                        if (src < W) all = all && got[src].y == xseq;
+                    if (all) break;
+                    if ((++rounds & 255u) == 0) {
+                        const unsigned long long now = global_ns();
+                        if (t0 == 0) t0 = now;
+                        else if (now - t0 > kPeerTimeoutNs) { timed_out = true; break; }
                     }
-                    total += __uint_as_float(got.x);
+                }
+                total = 0.f;
+#pragma unroll
+                for (int src = 0; src < DDPB_MAX_PEERS; ++src)
+                    if (src < W) total += __uint_as_float(got[src].x);
+                if (timed_out) {
+                    job.state->reserved[0] = 1;
+                    if (own == P && loss_slot) *loss_slot = __uint_as_float(kTimeoutSentinel);
+                    if (own == P && gloss_slot) *gloss_slot = __uint_as_float(kTimeoutSentinel);
+                } else if (own == P && gloss_slot) {
+                    // mean loss over all ranks: what demo.py:112-121 obtains with two gloo all-reduces
+                    *gloss_slot = __fdiv_rn(total, __fmul_rn((float)B, (float)W));
                 }
             }
         }
-        if (owner) {
+        if (owner && !timed_out) {
             if (own == P) {
                 g_out[P] = total;                                            // sum (o-t)^2 (over all ranks when W > 1)
             } else {
@@ -441,7 +475,7 @@ toy_step_kernel(const __grid_constant__ JobList jl) {
                 }
             }
         }
-        if (cta == 0 && tid == kComputeThreads) {          // advance the device-resident counters
+        if (cta == 0 && tid == kComputeThreads && !timed_out) {          // advance the device-resident counters
             const long long seq_now = need_seq ? seq : job.state->seq;
             job.state->seq = seq_now + 1;
             if (mode == DDPB_MODE_STEP) job.state->step = step + 1;
@@ -620,6 +654,7 @@ static int launch_toy_step(const ddpb_toy_job *jobs, int njobs, cudaStream_t str
         if (!q.idx || q.n_data < 0 || (q.n_data & 3) || ((uintptr_t)q.x & 15) || ((uintptr_t)q.y & 15)) jl.jobs[j].n_data = 0;
     }
     toy_step_kernel<<<dim3(kCluster, njobs, 1), kThreads, 0, stream>>>(jl);
+    ddpb::count_launch();
     DDPB_CUDA(cudaGetLastError());
     return 0;
 }
@@ -635,6 +670,23 @@ DDPB_API int ddpb_toy_step_h2d(const ddpb_toy_job *jobs, int njobs, void *dst_de
         DDPB_CUDA(cudaMemcpyAsync(dst_dev, src_host, (size_t)bytes, cudaMemcpyHostToDevice, (cudaStream_t)stream));
     }
     return launch_toy_step(jobs, njobs, (cudaStream_t)stream);
+}
+
+DDPB_API int ddpb_toy_iteration(ddpb_toy_iter *it) {
+    DDPB_REQUIRE(it != nullptr, "ddpb_toy_iteration: null descriptor");
+    DDPB_REQUIRE(it->nwait >= 0 && it->nwait <= 2 * DDPB_MAX_JOBS, "ddpb_toy_iteration: nwait %d outside 0..%d", it->nwait,
+                 2 * DDPB_MAX_JOBS);
+    if (it->idx) {
+        if (int rc = ddpb_host_gather(it->X, it->Y, it->idx, it->B, it->dx, it->dy, it->out_x, it->out_y)) return rc;
+    }
+    if (it->njobs > 0)
+        if (int rc = launch_toy_step(it->jobs, it->njobs, (cudaStream_t)it->stream)) return rc;
+    for (int w = 0; w < it->nwait; ++w) {
+        DDPB_REQUIRE(it->wait_slot[w] != nullptr, "ddpb_toy_iteration: wait slot %d is null", w);
+        if (int rc = ddpb::wait_slot(it->wait_slot[w], it->sentinel_bits, it->spin_ns, (cudaStream_t)it->stream, &it->wait_value[w]))
+            return rc;
+    }
+    return 0;
 }
 
 // ---------------------------------------------------------------------------------------
@@ -659,6 +711,8 @@ DDPB_API int ddpb_toy_step_h2d(const ddpb_toy_job *jobs, int njobs, void *dst_de
 //     with that device current; make that first call before any stream capture begins.
 namespace {
 
+static_assert(DDPB_MAX_VIRTUAL_RANKS <= DDPB_MAX_JOBS && DDPB_MAX_VIRTUAL_RANKS <= DDPB_MAX_PEERS,
+              "every virtual rank is one job of the launch and one peer of the exchange");
 constexpr size_t kWindowBytes = DDPB_XCHG_WINDOW_BYTES;
 constexpr size_t kVirtualBytes = DDPB_MAX_VIRTUAL_RANKS * kWindowBytes;
 
@@ -667,18 +721,23 @@ static __device__ __align__(256) unsigned char g_virtual_windows[kVirtualBytes];
 
 // In host code `g_virtual_windows` is only a handle for the runtime, never an address a kernel
 // may use: the real device address comes from cudaGetSymbolAddress, per device.
-unsigned char *g_virtual_base[64] = {};
+// Host threads may race to fill an entry; they would all store the same address (the lookup is
+// idempotent), so a relaxed atomic is enough.  cudaDeviceReset invalidates the entries: a process that
+// resets a device must not call this entry point on it afterwards.
+std::atomic<unsigned char *> g_virtual_base[64] = {};
 
 int virtual_window_base(unsigned char **base_out) {
     int dev = -1;
     DDPB_CUDA(cudaGetDevice(&dev));
     DDPB_REQUIRE(dev >= 0 && dev < 64, "ddpb_toy_step_virtual_ranks: device index %d not supported", dev);
-    if (!g_virtual_base[dev]) {
+    unsigned char *base = g_virtual_base[dev].load(std::memory_order_relaxed);
+    if (!base) {
         void *ptr = nullptr;
         DDPB_CUDA(cudaGetSymbolAddress(&ptr, g_virtual_windows));
-        g_virtual_base[dev] = static_cast<unsigned char *>(ptr);
+        base = static_cast<unsigned char *>(ptr);
+        g_virtual_base[dev].store(base, std::memory_order_relaxed);
     }
-    *base_out = g_virtual_base[dev];
+    *base_out = base;
     return 0;
 }
 

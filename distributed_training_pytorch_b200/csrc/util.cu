@@ -1,5 +1,6 @@
 // Introspection, error text and thin copy/sync helpers of the C ABI.
 #include "common.cuh"
+#include <atomic>
 #include <cstring>
 
 namespace ddpb {
@@ -17,7 +18,12 @@ int fail(int code, const char *fmt, ...) {
     return code;
 }
 
+static std::atomic<long long> g_launches{0};
+void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+
 }  // namespace ddpb
+
+DDPB_API long long ddpb_launch_count(void) { return ddpb::g_launches.load(std::memory_order_relaxed); }
 
 DDPB_API int ddpb_version(void) { return DDPB_VERSION; }
 
@@ -88,8 +94,8 @@ DDPB_API int ddpb_graph_destroy(void *graph_exec) {
 // back to cudaStreamSynchronize so failures surface as CUDA errors, not as hangs.
 #include <chrono>
 
-DDPB_API int ddpb_wait_f32(const float *host_slot, uint32_t sentinel_bits, int64_t spin_ns, void *stream, float *out) {
-    DDPB_REQUIRE(host_slot && out, "ddpb_wait_f32: null argument");
+namespace ddpb {
+int wait_slot(const float *host_slot, unsigned sentinel_bits, long long spin_ns, cudaStream_t stream, float *out) {
     const volatile uint32_t *slot = reinterpret_cast<const volatile uint32_t *>(host_slot);
     uint32_t bits = *slot;
     if (bits == sentinel_bits) {
@@ -98,7 +104,7 @@ DDPB_API int ddpb_wait_f32(const float *host_slot, uint32_t sentinel_bits, int64
         while ((bits = *slot) == sentinel_bits) {
             if ((++spins & 63) == 0 &&
                 std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::steady_clock::now() - t0).count() > spin_ns) {
-                DDPB_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+                DDPB_CUDA(cudaStreamSynchronize(stream));
                 bits = *slot;
                 break;
             }
@@ -111,6 +117,12 @@ DDPB_API int ddpb_wait_f32(const float *host_slot, uint32_t sentinel_bits, int64
     cvt.u = bits;
     *out = cvt.f;
     return 0;
+}
+}  // namespace ddpb
+
+DDPB_API int ddpb_wait_f32(const float *host_slot, uint32_t sentinel_bits, int64_t spin_ns, void *stream, float *out) {
+    DDPB_REQUIRE(host_slot && out, "ddpb_wait_f32: null argument");
+    return ddpb::wait_slot(host_slot, sentinel_bits, spin_ns, (cudaStream_t)stream, out);
 }
 
 // ---- peer windows ------------------------------------------------------------------------

@@ -141,6 +141,7 @@ DDPB_API int ddpb_wide_first_fwd(const float *x, const int32_t *idx, const float
                                  float *act_t, int B, int H, int ld_t, void *stream) {
     DDPB_REQUIRE(x && W0 && b0 && act && act_t && B >= 1 && B <= kMaxB && H >= 1 && ld_t >= B, "ddpb_wide_first_fwd: bad arguments");
     first_fwd_kernel<<<grid_for((long long)B * H), 256, 0, (cudaStream_t)stream>>>(x, idx, W0, b0, act, act_t, B, H, ld_t);
+    ddpb::count_launch();
     DDPB_CUDA(cudaGetLastError());
     return 0;
 }
@@ -149,6 +150,7 @@ DDPB_API int ddpb_wide_last_fwd(const float *act3, const float *W4, const float 
                                 float *out, float *dz4, float *sq, int B, int H, void *stream) {
     DDPB_REQUIRE(act3 && W4 && b4 && out && B >= 1 && B <= kMaxB && H >= 1 && (!y || (dz4 && sq)), "ddpb_wide_last_fwd: bad arguments");
     last_fwd_kernel<<<B, 256, 0, (cudaStream_t)stream>>>(act3, W4, b4, y, idx, out, dz4, sq, B, H);
+    ddpb::count_launch();
     DDPB_CUDA(cudaGetLastError());
     return 0;
 }
@@ -160,6 +162,7 @@ DDPB_API int ddpb_wide_last_bwd(const float *act3, const float *W4, const float 
                  "ddpb_wide_last_bwd: bad arguments");
     last_bwd_kernel<<<(H + 31) / 32, 256, 0, (cudaStream_t)stream>>>(act3, W4, dz4, sq, dz3, dz3_t, gW4, gb4, sq_sum_out,
                                                                       loss_slot, B, H, ld_t);
+    ddpb::count_launch();
     DDPB_CUDA(cudaGetLastError());
     return 0;
 }
@@ -168,6 +171,7 @@ DDPB_API int ddpb_wide_first_bwd(const float *dz0, const float *x, const int32_t
                                  void *stream) {
     DDPB_REQUIRE(dz0 && x && gW0 && gb0 && B >= 1 && B <= kMaxB && H >= 1, "ddpb_wide_first_bwd: bad arguments");
     first_bwd_kernel<<<(H + 255) / 256, 256, 0, (cudaStream_t)stream>>>(dz0, x, idx, gW0, gb0, B, H);
+    ddpb::count_launch();
     DDPB_CUDA(cudaGetLastError());
     return 0;
 }

@@ -88,9 +88,9 @@ class HostBatch:
     """One half (data or target) of a staged batch in pinned host memory.
 
     Quacks like the pinned tensor the reference's DataLoader yields: .cuda()/.to(device)
-    hand back the device twin (one async H2D copy of the whole (x, y) block, issued together
-    with the step that consumes it), .size()/.shape describe it; any other attribute is
-    looked up on the pinned tensor itself."""
+    hand back the device-side handle (the toy kernel reads the pinned rows itself over PCIe; other
+    consumers get one async H2D copy of the whole (x, y) block), .size()/.shape describe it; any
+    other attribute is looked up on the pinned tensor itself."""
 
     __slots__ = ("stage", "which")
 
@@ -99,6 +99,7 @@ class HostBatch:
 
     @property
     def tensor(self):
+        self.stage.materialize()
         return self.stage.host[self.which]
 
     def cuda(self, device=None, non_blocking=False):
@@ -121,13 +122,13 @@ class HostBatch:
         return self.stage.B
 
     def __getattr__(self, name):
-        return getattr(self.stage.host[self.which], name)
+        return getattr(self.tensor, name)
 
 
 class StagedBatch:
-    """Device twin of a HostBatch.  The copy is deferred until the step that reads the batch
-    is launched (one host call does both); touching it as a tensor (`.tensor()` or any tensor
-    attribute) performs the copy immediately."""
+    """Device-side handle of a HostBatch.  Nothing moves when it is made: the fused toy step reads the
+    pinned rows in place, and a consumer that needs a real device tensor (`.tensor()` or any tensor
+    attribute) triggers the H2D copy of the block then."""
 
     __slots__ = ("stage", "which")
 
@@ -159,11 +160,31 @@ class StagedBatch:
         return getattr(self.tensor(), name)
 
 
-class _Stage:
-    """A pinned (x | y) block and its device twin; a DataLoader cycles through a few."""
+class _EventGuard:
+    __slots__ = ("events",)
 
-    def __init__(self, batch, dx, dy):
+    def __init__(self, events):
+        self.events = events
+
+    def synchronize(self):
+        for ev in self.events:
+            ev.synchronize()
+
+
+class _Stage:
+    """A pinned (x | y) block, the description of the rows that belong in it, and (on demand) its
+    device twin; a DataLoader cycles through a few.
+
+    The rows are gathered LAZILY: the loader only records which indices the block is to hold; the
+    gather runs inside the native call that launches the consuming step (engine.flush), or on the
+    first access to the host tensor.  A block is handed out again only after its last consumer has
+    run on the GPU (`wait_free`): the toy kernel reads the block in place, and the copies issued for
+    the other back ends are asynchronous, so without that wait a host that runs ahead of the GPU
+    would overwrite rows that are still to be read."""
+
+    def __init__(self, loader, batch, dx, dy):
         self.block = torch.empty(batch * (dx + dy), dtype=torch.float32, pin_memory=torch.cuda.is_available())
+        self.loader = loader
         self.batch, self.dx, self.dy = batch, dx, dy
         self.nbytes = self.block.numel() * 4
         self.host_ptr = self.block.data_ptr()
@@ -173,21 +194,25 @@ class _Stage:
         self.dblock = None
         self.dev_x_ptr = self.dev_y_ptr = 0
         self.copied = True          # nothing to copy yet
+        self.pending_idx = None     # (index array kept alive, address of the first index) until gathered
+        self.guard = None           # who still reads the block: (engine, launch number) or a CUDA event
         self.halves = (HostBatch(self, 0), HostBatch(self, 1))
         self.twins = (StagedBatch(self, 0), StagedBatch(self, 1))
+        self.B = -1
         self.set_rows(batch)
 
     def set_rows(self, B):
-        self.B = B
-        views = self._host_views.get(B)
-        if views is None:
-            views = (self.block[:B * self.dx].view(B, self.dx),
-                     self.block[self.batch * self.dx:self.batch * self.dx + B * self.dy].view(B, self.dy))
-            self._host_views[B] = views
-        self.host = views
+        if B != self.B:
+            self.B = B
+            views = self._host_views.get(B)
+            if views is None:
+                views = (self.block[:B * self.dx].view(B, self.dx),
+                         self.block[self.batch * self.dx:self.batch * self.dx + B * self.dy].view(B, self.dy))
+                self._host_views[B] = views
+            self.host = views
+            if self.dblock is not None:
+                self.dev = self._device_views(B)
         self.copied = False
-        if self.dblock is not None:
-            self.dev = self._device_views(B)
 
     def _device_views(self, B):
         views = self._dev_views.get(B)
@@ -197,26 +222,74 @@ class _Stage:
             self._dev_views[B] = views
         return views
 
+    # -- life cycle of one batch --------------------------------------------------------
+    def wait_free(self):
+        """Block until the GPU work that reads this block (in place or through its async copy) has run."""
+        g = self.guard
+        if g is not None:
+            self.guard = None
+            if type(g) is tuple:
+                engine, launch_no = g
+                if engine.completed < launch_no:
+                    engine.sync()
+            else:
+                g.synchronize()
+
+    def begin(self, B, idx, idx_addr):
+        """The block is to hold rows idx[...] (B of them, first index at address idx_addr)."""
+        if self.guard is not None:
+            self.wait_free()
+        self.set_rows(B)
+        self.pending_idx = (idx, idx_addr)
+
+    def materialize(self):
+        """Gather the rows now (host code, csrc/sampler.cu) unless a launch already did."""
+        p = self.pending_idx
+        if p is not None:
+            self.pending_idx = None
+            ld = self.loader
+            if _lib.lib().ddpb_host_gather(ld.x_ptr, ld.y_ptr, p[1], self.B, self.dx, self.dy, self.host_x_ptr, self.host_y_ptr):
+                _lib.check(1, "ddpb_host_gather")
+
     def staged(self, device=None):
-        if self.dblock is None or (device is not None and torch.device(device).index not in (None, self.device)):
+        if self.device is None:
             idx = torch.cuda.current_device() if device is None else torch.device(device).index
-            idx = torch.cuda.current_device() if idx is None else idx
-            self.device = idx
-            self.dblock = torch.empty_like(self.block, device=f"cuda:{idx}")
+            self.device = torch.cuda.current_device() if idx is None else idx
+        elif device is not None:
+            idx = torch.device(device).index
+            if idx is not None and idx != self.device:
+                self.device, self.dblock = idx, None
+        return self.twins
+
+    def _twin(self):
+        if self.dblock is None:
+            self.dblock = torch.empty_like(self.block, device=f"cuda:{self.device}")
             self.dev_x_ptr = self.dblock.data_ptr()
             self.dev_y_ptr = self.dev_x_ptr + self.batch * self.dx * 4
             self._dev_views = {}
             self.dev = self._device_views(self.B)
-        return self.twins
 
     def copy_now(self):
-        """Issue the H2D copy on the current stream unless a step launch already carried it."""
+        """Gather (if still pending) and issue the H2D copy of the block on the engine's stream, once."""
         if not self.copied:
             from .engine import engine_for
+            if self.device is None:
+                self.device = torch.cuda.current_device()
+            self._twin()
+            self.materialize()
             eng = engine_for(self.device)
-            eng.drop_pending_copy(self)
             _lib.check(eng.lib.ddpb_memcpy_h2d_async(self.dev_x_ptr, self.host_ptr, self.nbytes, eng.stream()), "h2d")
             self.copied = True
+            self.guard_with_event(eng.torch_stream())
+
+    def guard_with_event(self, *torch_streams):
+        """The block must not be refilled before what has been enqueued on these streams so far has run."""
+        events = getattr(self, "_events", None)
+        if events is None or len(events) != len(torch_streams):
+            events = self._events = [torch.cuda.Event() for _ in torch_streams]
+        for ev, st in zip(events, torch_streams):
+            ev.record(st)
+        self.guard = _EventGuard(events)
 
 
 class DeviceBatch:
@@ -272,6 +345,7 @@ class DataLoader:
         self.num_workers, self.pin_memory = num_workers, pin_memory
         self.x, self.y = _dense(dataset)
         self.dx, self.dy = self.x.shape[1], self.y.shape[1]
+        self.x_ptr, self.y_ptr = self.x.data_ptr(), self.y.data_ptr()
         if device_resident is None:
             device_resident = os.environ.get("DDPB_DEVICE_DATA", "0") == "1"
         self.device_resident = bool(device_resident)
@@ -298,11 +372,10 @@ class DataLoader:
 
     def _iter_host(self):
         if self._stages is None:
-            self._stages = [_Stage(self.batch_size, self.dx, self.dy) for _ in range(self.STAGES)]
+            self._stages = [_Stage(self, self.batch_size, self.dx, self.dy) for _ in range(self.STAGES)]
         idx = self._indices()
         n, bs = len(idx), self.batch_size
-        gather = _lib.lib().ddpb_host_gather
-        xp, yp, idx_ptr, dx, dy = self.x.data_ptr(), self.y.data_ptr(), idx.ctypes.data, self.dx, self.dy
+        idx_addr = idx.ctypes.data
         stages, nstages = self._stages, self.STAGES
         for start in range(0, n, bs):
             B = min(bs, n - start)
@@ -311,9 +384,7 @@ class DataLoader:
             k = self._next_stage
             stage = stages[k]
             self._next_stage = k + 1 if k + 1 < nstages else 0
-            stage.set_rows(B)
-            if gather(xp, yp, idx_ptr + start * 8, B, dx, dy, stage.host_x_ptr, stage.host_y_ptr):
-                _lib.check(1, "ddpb_host_gather")
+            stage.begin(B, idx, idx_addr + start * 8)       # rows are gathered by the call that launches the step
             yield stage.halves
 
     def _iter_device(self):

@@ -24,6 +24,7 @@ import torch.distributed as dist
 from . import _lib
 import ctypes
 import os
+import weakref
 
 import numpy as np
 
@@ -31,10 +32,28 @@ from .data import DeviceBatch, HostBatch, StagedBatch
 from .engine import engine_for
 from .toy_model_and_data import MultiGPUModel, ToyModel
 
-_OWNERS = {}          # id(nn.Parameter) -> backend
+_OWNERS = weakref.WeakValueDictionary()          # id(nn.Parameter) -> backend (alive as long as its wrapper)
 LOSS_RING = 1024      # loss slots per model; a LossValue stays readable for this many steps
-LOSS_SENTINEL = 0x7FC0DEAD   # a NaN payload no kernel produces: "slot not written yet"
+LOSS_SENTINEL = _lib.LOSS_SENTINEL
+LOSS_TIMEOUT = _lib.LOSS_TIMEOUT_BITS
 LOSS_SPIN_NS = 200_000       # poll this long before falling back to a stream synchronisation
+ZERO_COPY_ROWS = 1024        # loader batches up to this many rows are read by the kernel straight from pinned memory
+PEER_CHECK_EVERY = 1024      # steps between looks at the device-side time-out flag when nobody reads losses
+_SECOND_BACKWARD = ("a second backward() reached this model before optimizer.step() or zero_grad(): torch would "
+                    "ACCUMULATE the two gradients in .grad, this package's gradient bucket is overwritten by every "
+                    "backward. Gradient accumulation is not part of the reference loop (demo.py:100-111) and is "
+                    "rejected rather than approximated")
+
+
+LOCAL_ONLY = object()   # process_group=LOCAL_ONLY: this wrapper is not replicated across processes (no collectives),
+                        # whatever torch.distributed says -- e.g. one rank of a job driving a model of its own
+
+
+def _world_of(process_group):
+    """(world, rank, backend name) the wrapper replicates over."""
+    if process_group is LOCAL_ONLY or not (dist.is_available() and dist.is_initialized()):
+        return 1, 0, None
+    return dist.get_world_size(process_group), dist.get_rank(process_group), dist.get_backend(process_group)
 
 
 def owner_of(param):
@@ -47,6 +66,8 @@ def owner_of(param):
 
 class Output:
     """Lazy result of wrapper(data).  Holds the batch; values exist after `.tensor()`."""
+
+    __slots__ = ("backend", "data")
 
     def __init__(self, backend, data):
         self.backend, self.data = backend, data
@@ -159,11 +180,8 @@ class ToyBackend:
             self._loss_out = ctypes.c_float()
             self._loss_out_ref = ctypes.byref(self._loss_out)
             self.m = self.v = None
-        self.world, self.rank, self.backend_name = 1, 0, None
         self.process_group = process_group
-        if dist.is_available() and dist.is_initialized():
-            self.world, self.rank = dist.get_world_size(process_group), dist.get_rank(process_group)
-            self.backend_name = dist.get_backend(process_group)
+        self.world, self.rank, self.backend_name = _world_of(process_group)
         self._sync_replicas()
         self.fused_exchange = False     # W > 1: gradient all-reduce fused into the step kernel (peer windows)
         self.peer = None
@@ -173,15 +191,25 @@ class ToyBackend:
         self.unread = 0                 # losses described since the last one was read
         self.ring_on_host = True
         self.waiting = None             # Loss whose backward() was called and not yet described
+        self.last_loss = None           # Loss of the most recently described job
         self.grads_fresh = False        # a GRAD job was described; an optimizer step may consume it
         self.keep = []                  # tensors referenced by the described job
-        self.job = _lib.ToyJob()
+        self.bound = None               # the loader block / batch handle the job currently points at
+        self.slot, self.job = self.engine.job_slot(self)
         j = self.job
         j.params, j.grads = self.params.data_ptr(), self.grads.data_ptr()
         j.state, j.loss_ring, j.loss_ring_n = self.state.data_ptr(), self.loss_ptr, LOSS_RING
         j.idx_rows, j.idx_stride = 1, 0
         j.world, j.rank, j.inv_world = 1, 0, 1.0
+        j.mode = -1
+        self._mode = -1
         self._out = None
+        # the mean loss over all ranks (demo.py:112-121), a by-product of the fused exchange or of the
+        # bucket all-reduce: pinned ring the GPU writes / a 4-byte async copy lands in
+        self.gloss_host = self.gloss_bits = None
+        if self.world > 1:
+            self.gloss_host = torch.zeros(LOSS_RING, dtype=torch.float32, pin_memory=True)
+            self.gloss_bits = self.gloss_host.numpy().view(np.uint32)
         if self.world > 1 and os.environ.get("DDPB_ALLREDUCE", "p2p") == "p2p" and lazy_step is not False:
             self._map_peer_windows()
 
@@ -240,13 +268,18 @@ class ToyBackend:
         for r, ptr in enumerate(mapped):
             j.peer_data[r] = ptr
         j.world, j.rank, j.inv_world = self.world, self.rank, 1.0 / self.world
+        j.global_loss_ring = self.gloss_host.data_ptr()
         self.fused_exchange = True
         self.lazy = True
 
     def check_peers(self):
         """Raise if a fused exchange timed out waiting for a peer (state.reserved[0] set by the kernel)."""
         if self.fused_exchange and int(self.state[2].item()) != 0:
-            raise _lib.DdpB200Error("a peer GPU did not deliver its gradient slice in time (fused all-reduce timed out)")
+            self._peer_timeout()
+
+    def _peer_timeout(self):
+        raise _lib.DdpB200Error("a peer GPU did not deliver its gradient slice within 2 s: the fused all-reduce gave up; "
+                                "parameters and optimizer state are those of the last completed step")
 
     # -- optimizer binding -----------------------------------------------------------
     def attach_optimizer(self, kind, hyper):
@@ -269,6 +302,7 @@ class ToyBackend:
 
     def optimizer_state_dict(self):
         self.engine.flush()
+        self.check_peers()
         return {"step": int(self.state[0].item()), "exp_avg": self.m, "exp_avg_sq": self.v}
 
     # -- describing work ---------------------------------------------------------------
@@ -278,15 +312,25 @@ class ToyBackend:
             data = data.cuda(self.device)
         if type(target) is HostBatch:
             target = target.cuda(self.device)
-        if type(data) is StagedBatch:                       # the loader's own batch: trusted layout, deferred copy
+        if type(data) is StagedBatch:                       # the loader's own batch: trusted layout
             stage = data.stage
             if target is not None and (type(target) is not StagedBatch or target.stage is not stage):
                 raise _lib.DdpB200Error("data and target must come from the same loader batch")
-            j.x, j.y, j.idx, j.B, j.idx_stride, j.n_data = stage.dev_x_ptr, stage.dev_y_ptr, None, stage.B, 0, 0
-            if not stage.copied:
-                self.engine.attach_copy(stage)
+            if stage.B <= ZERO_COPY_ROWS:
+                # the kernel reads the pinned rows in place (mapped host memory, one PCIe round trip
+                # inside the launch) -- this IS the `.cuda()` of demo.py:102-103; the rows themselves
+                # are gathered by the native call that launches the step
+                if self.bound is not stage or j.B != stage.B:
+                    j.x, j.y, j.idx, j.B, j.idx_stride, j.n_data = stage.host_x_ptr, stage.host_y_ptr, None, stage.B, 0, 0
+                    self.bound = stage
+                self.engine.attach_stage(stage)
+            else:
+                stage.copy_now()                           # large batches: one async H2D copy of the block
+                j.x, j.y, j.idx, j.B, j.idx_stride, j.n_data = stage.dev_x_ptr, stage.dev_y_ptr, None, stage.B, 0, 0
+                self.bound = None
             self.keep = stage
             return
+        self.bound = None
         if type(data) is DeviceBatch:
             j.x, j.y, j.idx, j.B = data.x.data_ptr(), data.y.data_ptr(), data.idx_ptr, data.B
             j.idx_stride, j.n_data = data.B, data.x.shape[0]
@@ -310,16 +354,27 @@ class ToyBackend:
 
     def _describe(self, loss, mode):
         self._bind_batch(loss.output.data, loss.target)
-        self.job.mode = mode
-        slot = loss.slot = self.seq % LOSS_RING
+        if mode != self._mode:
+            self.job.mode = self._mode = mode
+        seq = self.seq
+        slot = loss.slot = seq % LOSS_RING
+        loss.batch = self.job.B
         if self.unread > 8:                      # nobody has been reading losses: keep them on the device
             if self.ring_on_host:
                 self.ring_on_host, self.job.loss_ring = False, self.loss_dev.data_ptr()
+                if self.fused_exchange:
+                    self.job.global_loss_ring = None
+            if self.fused_exchange and (seq % PEER_CHECK_EVERY) == PEER_CHECK_EVERY - 1:
+                self.engine.flush()
+                self.check_peers()               # nobody polls the loss ring, so look at the device flag now and then
         else:
             self.unread += 1
             self.loss_bits[slot] = LOSS_SENTINEL
+            if self.gloss_bits is not None:
+                self.gloss_bits[slot] = LOSS_SENTINEL
         loss.on_host = self.ring_on_host
-        self.seq += 1
+        self.last_loss = loss
+        self.seq = seq + 1
         self.grads_fresh = mode == _lib.MODE_GRAD
         self.engine.enqueue(self)
         if self.world > 1 and mode == _lib.MODE_GRAD:
@@ -327,29 +382,33 @@ class ToyBackend:
 
     def after_launch(self, stream):
         """Called by the engine right after the fused kernel of this model went out."""
-        self.keep = []
-        if self.world > 1 and self.job.mode == _lib.MODE_GRAD and self._sync_grads:
+        self.keep = None
+        if self.world > 1 and self._mode == _lib.MODE_GRAD and self._sync_grads:
             self._allreduce_bucket(stream)
 
     _sync_grads = True
 
     def _allreduce_bucket(self, stream):
         n = self.P + 1                    # the loss sum rides in the bucket's last element
+        lib = self.engine.lib
         if self.backend_name == "nccl":
-            _lib.check(self.engine.lib.ddpb_allreduce_sum_f32(self.engine.comm, self.grads.data_ptr(), n, stream),
-                       "ddpb_allreduce_sum_f32")
+            _lib.check(lib.ddpb_allreduce_sum_f32(self.engine.comm, self.grads.data_ptr(), n, stream), "ddpb_allreduce_sum_f32")
         else:
             host = self.grads.cpu()
             dist.all_reduce(host, group=self.process_group)
             self.grads.copy_(host)
+        loss = self.last_loss
+        if loss is not None and loss.on_host:    # sum_r sum_b (o-t)^2 for the logged mean: 4 bytes, asynchronously
+            _lib.check(lib.ddpb_memcpy_d2h_async(self.gloss_host.data_ptr() + 4 * loss.slot,
+                                                 self.grads.data_ptr() + 4 * self.P, 4, stream), "d2h")
+            loss.global_is_sum = True
 
     def request_backward(self, loss):
-        if self.waiting is not None and self.waiting is not loss:
-            self._describe(self.waiting, _lib.MODE_GRAD)      # an earlier backward never got its step
+        if (self.waiting is not None and self.waiting is not loss) or self.grads_fresh:
+            raise NotImplementedError(_SECOND_BACKWARD)
         if self.lazy and self.opt_kind is not None:
             self.waiting = loss                               # decide GRAD vs STEP when step() or a read arrives
         else:
-            self.waiting = None
             self._describe(loss, _lib.MODE_GRAD)
 
     def discard_pending_backward(self):
@@ -357,12 +416,13 @@ class ToyBackend:
         self.grads_fresh = False
 
     def request_step(self):
-        if self.opt_kind is None:
-            raise _lib.DdpB200Error("no optimizer attached")
-        if self.waiting is not None:
-            loss, self.waiting = self.waiting, None
+        loss = self.waiting
+        if loss is not None:
+            self.waiting = None
             self._describe(loss, _lib.MODE_STEP)
             return
+        if self.opt_kind is None:
+            raise _lib.DdpB200Error("no optimizer attached")
         if not self.grads_fresh:
             return                                            # torch skips parameters whose grad is None
         self.grads_fresh = False
@@ -375,13 +435,12 @@ class ToyBackend:
                                                    h["eps"], self.job.bias_table, self.job.bias_table_n,
                                                    self.state.data_ptr(), 1, stream),
                        "ddpb_fused_avg_adam_dev")
-            self.engine.launches += 2
         else:
-            self._sgd_steps = getattr(self, "_sgd_steps", 0) + 1
-            _lib.check(lib.ddpb_fused_avg_sgd(self.grads.data_ptr(), self.params.data_ptr(), self.m.data_ptr(), self.P,
-                                              scale, h["lr"], h["momentum"], self._sgd_steps, stream),
-                       "ddpb_fused_avg_sgd")
-            self.engine.launches += 1
+            # the device-resident step counter decides "first step", as in the fused kernel, so the
+            # two paths can be mixed freely (momentum buffer initialised exactly once)
+            _lib.check(lib.ddpb_fused_avg_sgd_dev(self.grads.data_ptr(), self.params.data_ptr(), self.m.data_ptr(), self.P,
+                                                  scale, h["lr"], h["momentum"], self.state.data_ptr(), 1, stream),
+                       "ddpb_fused_avg_sgd_dev")
 
     # -- reading results ----------------------------------------------------------------
     def _ensure_described(self, loss):
@@ -390,26 +449,72 @@ class ToyBackend:
                 self.waiting = None
             self._describe(loss, _lib.MODE_GRAD)
 
+    def _value(self, loss):
+        """The local mean loss of `loss` as a Python float (launches / waits as needed)."""
+        v = loss.value
+        if v is None:
+            if loss.slot is None:
+                self._ensure_described(loss)
+            eng = self.engine
+            if eng.queue:
+                # launch (+ wait, in the same native call, when the newest step is the one being read; an
+                # older loss has long arrived and must not make the host wait for the step just launched)
+                eng.flush(loss is self.last_loss)
+                v = loss.value
+            self.unread = 0
+            if not self.ring_on_host:            # from the next step on, losses go straight to host memory again
+                self.ring_on_host, self.job.loss_ring = True, self.loss_ptr
+                if self.fused_exchange:
+                    self.job.global_loss_ring = self.gloss_host.data_ptr()
+            if v is None:
+                if not loss.on_host:             # this one was written to HBM: copy it out the classic way
+                    off = 4 * loss.slot
+                    _lib.check(eng.lib.ddpb_memcpy_d2h_async(self.loss_ptr + off, self.loss_dev.data_ptr() + off, 4, eng.last_stream), "d2h")
+                    eng.sync()
+                    v = float(self.loss_host[loss.slot])
+                else:
+                    rc = eng.lib.ddpb_wait_f32(self.loss_ptr + 4 * loss.slot, LOSS_SENTINEL, LOSS_SPIN_NS, eng.last_stream,
+                                               self._loss_out_ref)
+                    if rc:
+                        _lib.check(rc, "ddpb_wait_f32")
+                    v = self._loss_out.value
+                loss.value = v
+        else:
+            self.unread = 0
+        if v != v and self.fused_exchange and int(self.loss_bits[loss.slot]) == LOSS_TIMEOUT:
+            self._peer_timeout()                 # the kernel wrote the time-out sentinel instead of a loss
+        return v
+
     def read_loss(self, loss):
         """Local mean loss as a 0-dim CPU tensor; blocks like the reference's .cpu() (demo.py:115)."""
-        if loss.slot is None:
-            self._ensure_described(loss)
+        a = np.empty((), np.float32)
+        a[()] = self._value(loss)
+        return torch.from_numpy(a)
+
+    def read_global_loss(self, loss):
+        """Mean loss over ALL ranks as a 0-dim CPU tensor -- the value demo.py:112-121 logs -- without a
+        host collective: the squared-error sum rides in the gradient bucket (element 371), so the
+        gradient exchange has already reduced it."""
+        if self.world == 1:
+            return self.read_loss(loss)
+        v = self._value(loss)                    # launches; the global value lands right after the local one
+        if not loss.on_host:
+            raise _lib.DdpB200Error("this loss was produced while nobody was reading losses (kept in HBM); read "
+                                    "losses regularly or call .cpu() for the local value")
+        if not (self.fused_exchange or loss.global_is_sum):
+            raise _lib.DdpB200Error("no reduced loss for this step: it took no gradient exchange (backward only)")
         eng = self.engine
-        if eng.queue:
-            eng.flush()
-        self.unread = 0
-        if not self.ring_on_host:                # from the next step on, losses go straight to host memory again
-            self.ring_on_host, self.job.loss_ring = True, self.loss_ptr
-        if not loss.on_host:                     # this one was written to HBM: copy it out the classic way
-            off = 4 * loss.slot
-            _lib.check(eng.lib.ddpb_memcpy_d2h_async(self.loss_ptr + off, self.loss_dev.data_ptr() + off, 4, eng.last_stream), "d2h")
-            _lib.check(eng.lib.ddpb_stream_sync(eng.last_stream), "ddpb_stream_sync")
-            return self.loss_host[loss.slot].clone()
-        rc = eng.lib.ddpb_wait_f32(self.loss_ptr + 4 * loss.slot, LOSS_SENTINEL, LOSS_SPIN_NS, eng.last_stream,
+        rc = eng.lib.ddpb_wait_f32(self.gloss_host.data_ptr() + 4 * loss.slot, LOSS_SENTINEL, LOSS_SPIN_NS, eng.last_stream,
                                    self._loss_out_ref)
         if rc:
             _lib.check(rc, "ddpb_wait_f32")
-        return torch.tensor(self._loss_out.value)
+        a = np.empty((), np.float32)
+        a[()] = self._loss_out.value
+        if loss.global_is_sum:                   # NCCL / gloo route: the all-reduced sum; the mean is formed here
+            a /= np.float32(loss.batch * self.world)
+        elif int(self.gloss_bits[loss.slot]) == LOSS_TIMEOUT:
+            self._peer_timeout()
+        return torch.from_numpy(a)
 
     def loss_device_view(self, loss):
         return self.read_loss(loss).to(self.device)
@@ -420,7 +525,9 @@ class ToyBackend:
         self._bind_batch(data, None)
         B = self.job.B
         out = torch.empty(B, 1, dtype=torch.float32, device=self.device)
-        self.job.out, self.job.mode = out.data_ptr(), _lib.MODE_FWD
+        self.job.out = out.data_ptr()
+        self.job.mode = self._mode = _lib.MODE_FWD
+        self.last_loss = None
         self.engine.enqueue(self)
         self.engine.flush()
         return out

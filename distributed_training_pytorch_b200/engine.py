@@ -8,6 +8,7 @@ ddpb_toy_step launch (blockIdx.y = model), so demo.py's two models cost one laun
 iteration on a single rank.
 """
 import ctypes
+import weakref
 
 import torch
 
@@ -40,14 +41,44 @@ class Engine:
             raise _lib.DdpB200Error(f"device {device_index} is sm_{major.value}{minor.value}; this library is built "
                                     "for sm_100a (B200) only")
         self.sm_count = sms.value
-        self.queue = []                                    # FlatModel objects with a described, unlaunched job
+        self.queue = []                                    # backends with a described, unlaunched job
+        # Job slots: every toy model of the device owns one element of this array and describes its
+        # work in place, so a launch of models in slot order passes the array as it is (no copies).
         self.jobs = (_lib.ToyJob * _lib.MAX_JOBS)()
-        self.launches = 0                                  # kernels this engine has launched (bench: gpu_launches)
-        self.pending_copy = None                           # a data._Stage whose H2D copy rides with the next launch
+        self._jobs_addr = ctypes.addressof(self.jobs)
+        self._job_size = ctypes.sizeof(_lib.ToyJob)
+        self._free_slots = list(range(_lib.MAX_JOBS))
+        self._scratch = (_lib.ToyJob * _lib.MAX_JOBS)()    # launches that are not a run of consecutive slots
+        self._scratch_addr = ctypes.addressof(self._scratch)
+        # the descriptor of ddpb_toy_iteration: gather + launch + loss wait in ONE host call
+        self.it = it = _lib.ToyIter()
+        self._it_addr = ctypes.addressof(it)
+        it.sentinel_bits, it.spin_ns = _lib.LOSS_SENTINEL, 200_000
+        self._iteration = self.lib.ddpb_toy_iteration
+        self.pending_stage = None                          # a data._Stage whose gather rides with the next launch
         self.last_stream = None                            # stream of the most recent launch
         self._stream = None
+        self._torch_stream = None
+        self.launch_no = 0                                 # toy launches issued / known to have run on the GPU
+        self.completed = 0
         self.comm = None                                   # NCCL communicator handle (void*)
         self.comm_rank, self.comm_world = 0, 1
+
+    @property
+    def launches(self):
+        """Kernels the library has launched in this process (counted at the launch sites, csrc/util.cu)."""
+        return int(self.lib.ddpb_launch_count())
+
+    def job_slot(self, owner):
+        """A ddpb_toy_job for a new model: an element of the engine's array while there are free ones
+        (given back when `owner` is garbage-collected), else a private struct that is packed at launch."""
+        free = self._free_slots
+        if not free:
+            return -1, _lib.ToyJob()
+        k = free.pop(0)
+        ctypes.memset(self._jobs_addr + k * self._job_size, 0, self._job_size)
+        weakref.finalize(owner, free.append, k)
+        return k, self.jobs[k]
 
     # -- streams -------------------------------------------------------------
     def stream(self):
@@ -57,15 +88,29 @@ class Engine:
         s = self._stream
         if s is None:
             s = self._stream = torch.cuda.current_stream(self.device).cuda_stream
+            self.it.stream = s
         return s
+
+    def torch_stream(self):
+        """The same stream as a torch object (for event records)."""
+        ts = self._torch_stream
+        if ts is None:
+            h = self.stream()
+            ts = self._torch_stream = (torch.cuda.ExternalStream(h, device=self.device) if h
+                                       else torch.cuda.default_stream(self.device))
+        return ts
 
     def use_stream(self, stream=None):
         """Launch on `stream` (a torch.cuda.Stream) from now on; None = re-read torch's current stream."""
         self.flush()
         self._stream = None if stream is None else stream.cuda_stream
+        self._torch_stream = None
+        if self._stream is not None:
+            self.it.stream = self._stream
 
     def sync(self):
         _lib.check(self.lib.ddpb_stream_sync(self.stream()), "ddpb_stream_sync")
+        self.completed = self.launch_no
 
     # -- lazy queue ------------------------------------------------------------
     def enqueue(self, model):
@@ -75,35 +120,72 @@ class Engine:
         if len(self.queue) == _lib.MAX_JOBS:
             self.flush()
 
-    def attach_copy(self, stage):
-        """The next launch copies `stage` (pinned (x|y) block) to its device twin first."""
-        if self.pending_copy is not None and self.pending_copy is not stage:
-            self.pending_copy.copy_now()
-        self.pending_copy = stage
+    def attach_stage(self, stage):
+        """The next launch reads `stage` (a pinned (x|y) block) in place; its rows are gathered by the
+        same native call."""
+        prev = self.pending_stage
+        if prev is not stage:
+            if prev is not None:
+                prev.materialize()
+                prev.guard = (self, self.launch_no + 1)
+            self.pending_stage = stage
 
-    def drop_pending_copy(self, stage):
-        if self.pending_copy is stage:
-            self.pending_copy = None
-
-    def flush(self):
-        """Launch everything described so far (one kernel for all pending toy jobs)."""
-        if not self.queue:
+    def flush(self, wait=False):
+        """Launch everything described so far (one kernel for all pending toy jobs).  wait=True also
+        polls, inside the same native call, the pinned loss slots of the launched steps and leaves the
+        values on their Loss objects."""
+        batch = self.queue
+        if not batch:
             return
-        batch, self.queue = self.queue, []
-        jobs = self.jobs
-        for i, model in enumerate(batch):
-            jobs[i] = model.job
-        stream = self.last_stream = self.stream()
-        stage = self.pending_copy
-        if stage is not None and not stage.copied:
-            rc = self.lib.ddpb_toy_step_h2d(jobs, len(batch), stage.dev_x_ptr, stage.host_ptr, stage.nbytes, stream)
-            stage.copied = True
+        self.queue = []
+        n = len(batch)
+        it = self.it
+        s0 = batch[0].slot
+        addr = self._jobs_addr + s0 * self._job_size if s0 >= 0 else 0
+        for i in range(1, n):
+            if batch[i].slot != s0 + i:
+                addr = 0
+                break
+        if not addr:                                       # not a run of consecutive slots: pack them
+            for i, model in enumerate(batch):
+                self._scratch[i] = model.job
+            addr = self._scratch_addr
+        it.jobs, it.njobs = addr, n
+        stream = self.last_stream = self._stream or self.stream()
+        self.launch_no = launch_no = self.launch_no + 1
+        stage = self.pending_stage
+        if stage is not None:
+            self.pending_stage = None
+            stage.guard = (self, launch_no)
+            p = stage.pending_idx
+            if p is not None:
+                stage.pending_idx = None
+                ld = stage.loader
+                it.X, it.Y, it.idx, it.B, it.dx, it.dy = ld.x_ptr, ld.y_ptr, p[1], stage.B, stage.dx, stage.dy
+                it.out_x, it.out_y = stage.host_x_ptr, stage.host_y_ptr
+            else:
+                it.idx = None
         else:
-            rc = self.lib.ddpb_toy_step(jobs, len(batch), stream)
-        self.pending_copy = None
+            it.idx = None
+        nwait = 0
+        if wait:
+            for model in batch:
+                loss = model.last_loss
+                if loss is not None and loss.on_host and loss.value is None:
+                    it.wait_slot[nwait] = model.loss_ptr + 4 * loss.slot
+                    nwait += 1
+        it.nwait = nwait
+        rc = self._iteration(self._it_addr)
         if rc:
-            _lib.check(rc, "ddpb_toy_step")
-        self.launches += 1
+            _lib.check(rc, "ddpb_toy_iteration")
+        if nwait:
+            k = 0
+            for model in batch:
+                loss = model.last_loss
+                if loss is not None and loss.on_host and loss.value is None:
+                    loss.value = it.wait_value[k]
+                    k += 1
+            self.completed = launch_no
         for model in batch:
             model.after_launch(stream)
 

@@ -20,16 +20,19 @@ class MSELoss:
 class Loss:
     """A scalar that exists on the device once its step has been launched."""
 
+    __slots__ = ("output", "target", "backend", "slot", "on_host", "value", "batch", "global_is_sum")
+
     def __init__(self, output, target):
         self.output, self.target = output, target
         self.backend = output.backend
         self.slot = None           # ring slot once described to the engine
         self.on_host = True        # whether that slot is in the pinned host ring or the HBM ring
-        self.backward_called = False
+        self.value = None          # the local mean loss (Python float) once it has been read
+        self.batch = 0             # local batch size of the step
+        self.global_is_sum = False # the reduced value that lands on the host is the squared-error SUM
 
     # -- autograd-like surface ----------------------------------------------
     def backward(self):
-        self.backward_called = True
         self.backend.request_backward(self)
 
     def detach(self):
@@ -93,11 +96,23 @@ class LossValue:
     """Result of loss.detach(): still lazy; .cpu() is the synchronisation point
     (demo.py:115,117), exactly where the reference blocks on its D2H copy."""
 
+    __slots__ = ("_loss",)
+
     def __init__(self, loss):
         self._loss = loss
 
     def cpu(self):
         return self._loss.backend.read_loss(self._loss)
+
+    def global_mean(self):
+        """0-dim CPU tensor: the mean loss over ALL ranks, sum_r(loss_r * B) / (B * W) -- what
+        demo.py:112-121 computes with two gloo all-reduces per step.  Here it is a by-product of the
+        gradient exchange (the squared-error sum is element 371 of the bucket): no host collective.
+        Like the reference's formula it assumes the same batch size on every rank (demo.py:113)."""
+        backend = self._loss.backend
+        if not hasattr(backend, "read_global_loss"):
+            raise NotImplementedError(f"{type(backend).__name__} does not carry the loss in its gradient bucket")
+        return backend.read_global_loss(self._loss)
 
     def item(self):
         return float(self.cpu())

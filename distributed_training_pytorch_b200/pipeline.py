@@ -77,7 +77,6 @@ class _Stage:
         with torch.cuda.device(self.device):
             stream = torch.cuda.current_stream(self.device).cuda_stream
             _lib.check(self.engine.lib.ddpb_segment_step(ctypes.byref(self.job), stream), "ddpb_segment_step")
-        self.engine.launches += 1
 
 
 class PipelineBackend:
@@ -91,10 +90,8 @@ class PipelineBackend:
         if self.dev0 != self.dev1:
             _lib.check(self.engine.lib.ddpb_enable_peer(self.dev0.index, self.dev1.index), "ddpb_enable_peer")
         self.process_group = process_group
-        self.world, self.rank, self.backend_name = 1, 0, None
-        if dist.is_available() and dist.is_initialized():
-            self.world, self.rank = dist.get_world_size(process_group), dist.get_rank(process_group)
-            self.backend_name = dist.get_backend(process_group)
+        from .ddp import _world_of
+        self.world, self.rank, self.backend_name = _world_of(process_group)
         self._sync_replicas()
         self.loss_host = torch.zeros(LOSS_RING, dtype=torch.float32, pin_memory=True)
         self.loss_bits = self.loss_host.numpy().view(np.uint32)
@@ -153,12 +150,15 @@ class PipelineBackend:
             stage = data.stage
             B = stage.B
             self._buffers(B)
+            stage.materialize()                       # the loader gathers lazily
             with torch.cuda.device(self.dev0):
                 _lib.check(lib.ddpb_memcpy_h2d_async(self.x0.data_ptr(), stage.host_x_ptr, B * stage.dx * 4,
                                                      torch.cuda.current_stream(self.dev0).cuda_stream), "h2d x")
             with torch.cuda.device(self.dev1):
                 _lib.check(lib.ddpb_memcpy_h2d_async(self.y1.data_ptr(), stage.host_y_ptr, B * stage.dy * 4,
                                                      torch.cuda.current_stream(self.dev1).cuda_stream), "h2d y")
+            # the pinned block may be refilled only after both asynchronous copies have run
+            stage.guard_with_event(torch.cuda.current_stream(self.dev0), torch.cuda.current_stream(self.dev1))
             return B, self.x0, self.y1
         if isinstance(target, (HostBatch, StagedBatch)):
             target = target.tensor if isinstance(target, HostBatch) else target.tensor()
@@ -203,9 +203,37 @@ class PipelineBackend:
                     dist.all_reduce(host, group=self.process_group)
                     st.grads.copy_(host)
 
+    def timed_split(self, x, y, reps):
+        """Median host-side latency (us) of the three launches of one iteration when each is waited for
+        before the next is issued: stage-0 forward (its stores carry the activation to dev1), stage-1
+        forward+backward+Adam (its stores carry the gradient back), stage-0 backward+Adam.  Launch and
+        stream-synchronisation overhead are inside each figure, so the sum exceeds a pipelined step."""
+        import time
+        j0, j1 = self.stage0.job, self.stage1.job
+        B = x.shape[0]
+        self._buffers(B)
+        out = []
+        for _ in range(reps):
+            t = [time.perf_counter()]
+            j0.B, j0.x, j0.out, j0.d_out, j0.d_in = B, x.data_ptr(), self.act.data_ptr(), None, None
+            self.stage0.launch(_lib.MODE_FWD)
+            torch.cuda.synchronize(self.dev0); t.append(time.perf_counter())
+            j1.B, j1.x, j1.y, j1.d_in = B, self.act.data_ptr(), y.data_ptr(), self.dact.data_ptr()
+            self.stage1.launch(_lib.MODE_STEP)
+            torch.cuda.synchronize(self.dev1); t.append(time.perf_counter())
+            j0.d_out = self.dact.data_ptr()
+            self.stage0.launch(_lib.MODE_STEP)
+            torch.cuda.synchronize(self.dev0); t.append(time.perf_counter())
+            out.append([(b - a) * 1e6 for a, b in zip(t, t[1:])])
+            self.seq += 1
+        med = np.median(np.asarray(out), axis=0)
+        return {"stage0_forward": float(med[0]), "stage1_forward_backward_adam": float(med[1]),
+                "stage0_backward_adam": float(med[2]), "note": "each phase = launch + stream synchronisation, host clock"}
+
     def request_backward(self, loss):
-        if self.waiting is not None and self.waiting is not loss:
-            self._run(self.waiting, _lib.MODE_GRAD)
+        if (self.waiting is not None and self.waiting is not loss) or self.grads_fresh:
+            from .ddp import _SECOND_BACKWARD
+            raise NotImplementedError(_SECOND_BACKWARD)
         if self.world == 1 and self.opt_kind is not None:
             self.waiting = loss
         else:

@@ -64,10 +64,8 @@ class WideBackend:
         self.P = P = sum(p.numel() for p in tensors)
         assert P == 3 * H * H + 7 * H + 1
         self.process_group = process_group
-        self.world, self.rank, self.backend_name = 1, 0, None
-        if dist.is_available() and dist.is_initialized():
-            self.world, self.rank = dist.get_world_size(process_group), dist.get_rank(process_group)
-            self.backend_name = dist.get_backend(process_group)
+        from .ddp import _world_of
+        self.world, self.rank, self.backend_name = _world_of(process_group)
         self.peer = None
         with torch.cuda.device(dev):
             if not self._map_peer_windows():
@@ -195,7 +193,6 @@ class WideBackend:
         j = self.bucket_jobs[index]
         j.ticket, j.mode, j.advance = self.ticket, int(reduce), int(advance)
         _lib.check(self.lib.ddpb_bucket_reduce_adam(ctypes.byref(j), stream), "ddpb_bucket_reduce_adam")
-        self.engine.launches += 1 + int(advance)
 
     def _sync_replicas(self):
         if self.world == 1:
@@ -245,11 +242,9 @@ class WideBackend:
                                                         h["betas"][1], h["eps"], self.bias_table.data_ptr(),
                                                         self.bias_table.shape[0], self.state.data_ptr(), int(advance),
                                                         stream), "ddpb_fused_avg_adam_dev")
-            self.engine.launches += 1 + int(advance)
         else:
             _lib.check(self.lib.ddpb_fused_avg_sgd(g, p, m, n, scale, h["lr"], h["momentum"], self.sgd_steps, stream),
                        "ddpb_fused_avg_sgd")
-            self.engine.launches += 1
 
     # -- the step ---------------------------------------------------------------------------
     def _bind(self, data, target):
@@ -300,7 +295,6 @@ class WideBackend:
         ck(lib.ddpb_wide_last_bwd(act[3].data_ptr(), w, self.dz4.data_ptr(), self.sq.data_ptr(), dz[0].data_ptr(),
                                   dz_t[0].data_ptr(), gw, gb, self.grads.data_ptr() + 4 * self.P, loss_slot, B, H, ld,
                                   stream), "last_bwd")
-        eng.launches += 6
         self._layer_done(4, with_update, None)
         main, side = torch.cuda.current_stream(self.device), self.side_stream
         cur = 0
@@ -314,10 +308,8 @@ class WideBackend:
             # the bucket's update overwrites W_l: it must follow wgrad (side) AND dgrad, which reads W_l (main)
             self._layer_done(l, with_update, side)
             cur += 1
-            eng.launches += 2
         gw, gb = self._g(0)
         ck(lib.ddpb_wide_first_bwd(dz[cur].data_ptr(), x, idx, gw, gb, B, H, stream), "first_bwd")
-        eng.launches += 1
         self._layer_done(0, with_update, None)
         main.wait_stream(side)
         self.keep = keep
@@ -359,8 +351,9 @@ class WideBackend:
                 self._update(start, n, cs, last)
 
     def request_backward(self, loss):
-        if self.waiting is not None and self.waiting is not loss:
-            self._run(self.waiting, False)
+        if (self.waiting is not None and self.waiting is not loss) or self.grads_fresh:
+            from .ddp import _SECOND_BACKWARD
+            raise NotImplementedError(_SECOND_BACKWARD)
         if self.opt_kind is not None:
             self.waiting = loss
         else:

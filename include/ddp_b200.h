@@ -33,12 +33,16 @@ extern "C" {
 #define DDPB_MAX_PEERS 8           /* GPUs of one NVSwitch box taking part in the fused exchange */
 #define DDPB_XCHG_ROW 376          /* 8-byte {value, ticket} slots per (parity, source rank) row (372 used) */
 #define DDPB_XCHG_WINDOW_BYTES (2 * DDPB_MAX_PEERS * DDPB_XCHG_ROW * 8)   /* one model's window per rank: 48 128 B */
+#define DDPB_LOSS_TIMEOUT_BITS 0x7FC0DEAEu       /* loss-slot value (NaN payload) after a peer time-out */
 
 /* ---- introspection ------------------------------------------------------- */
 int ddpb_version(void);
 const char *ddpb_last_error(void);
 /* device properties the host layer sizes its grids with (148 SMs on B200). */
 int ddpb_device_info(int device, int *cc_major, int *cc_minor, int *sm_count);
+/* kernels this library has launched in this process so far (every launch site counts itself);
+ * bench.py reports the difference over its timed region as gpu_launches. */
+long long ddpb_launch_count(void);
 
 /* ---- sampler: DistributedSampler(dataset, shuffle=True) ------------------- */
 /* demo.py:144 builds it, demo.py:96-98 reseeds it per epoch.  Host code, bit-exact
@@ -107,6 +111,9 @@ typedef struct ddpb_toy_job {
     const float *y;           /* [B,1] targets, or the whole dataset */
     const int32_t *idx;       /* NULL, or [idx_rows][idx_stride] sample indices; row = seq % idx_rows */
     float *out;               /* FWD: [B,1] */
+    float *global_loss_ring;  /* optional, world > 1 STEP: [loss_ring_n] slots for the mean loss over ALL ranks,
+                               * sum_r sum_b (o-t)^2 / (B * world) -- the value demo.py:112-121 logs after two gloo
+                               * all-reduces, here a by-product of the fused exchange (bucket element 371) */
     int32_t B;                /* local batch (1..65536) */
     int32_t mode;             /* DDPB_MODE_* */
     int32_t opt;              /* DDPB_OPT_* */
@@ -120,7 +127,10 @@ typedef struct ddpb_toy_job {
      * peer_data[r] is rank r's window as mapped into THIS process (ddpb_peer_alloc /
      * ddpb_peer_open), zero-initialised, DDPB_XCHG_WINDOW_BYTES bytes, 8-byte aligned; entry [rank]
      * is this rank's own window.  state->seq must advance in lock step on all ranks;
-     * state->reserved[0] != 0 afterwards = a peer timed out.  peer_flags is unused (reserved). */
+     * A peer that has not delivered its slices within ~2 s (global timer) makes the kernel give up
+     * loudly: state->reserved[0] = 1, the step's loss slot holds DDPB_LOSS_TIMEOUT_BITS (a NaN), and
+     * params / m / v / step / seq are left as they were (the step can be repeated).  Callers must look
+     * at one of the two; the Python layer raises.  peer_flags is unused (reserved). */
     float *peer_data[DDPB_MAX_PEERS];
     uint32_t *peer_flags[DDPB_MAX_PEERS];
     int32_t world, rank;
@@ -134,6 +144,31 @@ int ddpb_toy_step(const ddpb_toy_job *jobs /* host */, int njobs, void *stream);
 int ddpb_toy_step_h2d(const ddpb_toy_job *jobs, int njobs, void *dst_dev, const void *src_host,
                       int64_t bytes, void *stream);
 
+/* One host call per iteration of demo.py:99-118 (batch assembly, the step, the blocking loss read):
+ *   1. idx != NULL: gather rows idx[0..B) of the dense host dataset (X [n,dx], Y [n,dy]) into the pinned
+ *      staging rows out_x / out_y (ddpb_host_gather; replaces ToyData.__getitem__ x B + default_collate);
+ *   2. launch ddpb_toy_step(jobs, njobs) on `stream` -- a job whose x / y point at that pinned staging
+ *      reads its batch over PCIe itself (mapped pinned memory), which replaces the two `.cuda()` copies
+ *      of demo.py:102-103: no copy-engine operation, no second host call;
+ *   3. nwait > 0: poll the pinned loss slots wait_slot[0..nwait) (ddpb_wait_f32 semantics: sentinel,
+ *      spin_ns, then a stream synchronisation) and return their values in wait_value -- the
+ *      loss.detach().cpu() of demo.py:115,117.
+ * The struct lives in host memory owned by the caller and may be reused from call to call. */
+typedef struct ddpb_toy_iter {
+    const ddpb_toy_job *jobs;
+    void *stream;
+    const float *X, *Y;             /* dense host dataset (gather source) */
+    const int64_t *idx;             /* NULL: no gather */
+    float *out_x, *out_y;           /* pinned staging rows */
+    const float *wait_slot[2 * DDPB_MAX_JOBS];
+    int64_t B, spin_ns;
+    int32_t njobs, dx, dy, nwait;
+    uint32_t sentinel_bits;
+    float wait_value[2 * DDPB_MAX_JOBS];
+    int32_t reserved;
+} ddpb_toy_iter;
+int ddpb_toy_iteration(ddpb_toy_iter *it /* host */);
+
 /* No counterpart in the reference.  `nranks` replicas (2..DDPB_MAX_VIRTUAL_RANKS) of one model
  * on the CURRENT GPU take one fused data-parallel step in a single launch: jobs[r] is replica
  * r's job (DDPB_MODE_STEP, its own params/m/v/grads/state and its own batch; all replicas'
@@ -146,7 +181,11 @@ int ddpb_toy_step_h2d(const ddpb_toy_job *jobs, int njobs, void *dst_dev, const 
  * The array is shared by every call and keeps the previous call's contents: the windows in use
  * are cleared on `stream` first, and calls whose kernels overlap on the GPU race -- serialise
  * them.  The first call on each device looks the array's device address up; make that call
- * before starting any stream capture.  More than DDPB_MAX_VIRTUAL_RANKS replicas is an error. */
+ * before starting any stream capture.  (Host threads that make that first call at the same time all
+ * look up and record the same address, which is harmless; after cudaDeviceReset the recorded address
+ * is stale, so do not use this entry point on a device the process has reset.)  A replica that does
+ * not see the others' slices within ~2 s gives up as described for ddpb_toy_step: check
+ * state->reserved[0] of the replicas.  More than DDPB_MAX_VIRTUAL_RANKS replicas is an error. */
 #define DDPB_MAX_VIRTUAL_RANKS 4
 int ddpb_toy_step_virtual_ranks(const ddpb_toy_job *jobs /* host */, int nranks, void *stream);
 
@@ -227,6 +266,11 @@ int ddpb_fused_avg_adam_dev(const float *bucket, float *p, float *m, float *v, i
 /* SGD with optional momentum (north_star lists it beside Adam; torch:optim/sgd.py). */
 int ddpb_fused_avg_sgd(const float *bucket, float *p, float *buf, int64_t n, float grad_scale,
                        double lr, double momentum, int64_t step, void *stream);
+/* Same with the device-resident counter: state->step == 0 means "first step" (the momentum buffer is
+ * initialised with the gradient), exactly as the fused toy step reads it, so eager and fused steps of
+ * one model can be mixed; advance != 0 increments state->step afterwards. */
+int ddpb_fused_avg_sgd_dev(const float *bucket, float *p, float *buf, int64_t n, float grad_scale,
+                           double lr, double momentum, ddpb_opt_state *state, int advance, void *stream);
 
 /* ---- bucket all-reduce fused with the optimizer, over NVLink peer windows -------------------
  * Replaces, for one gradient bucket of a large model, the c10d Reducer's ncclAllReduce

@@ -112,3 +112,104 @@ def test_unsupported_models_fail_loudly():
         DDP(torch.nn.Linear(2, 2).cuda())
     with pytest.raises(b200.DdpB200Error):
         DDP(ToyModel())                            # still on the CPU
+
+
+def test_second_backward_without_step_is_rejected():
+    """torch accumulates .grad over backward() calls; this package's bucket is overwritten by each one.
+    The case is rejected loudly (NotImplementedError) instead of silently applying only the last
+    gradient -- in both the lazy (fused) and the eager mode; zero_grad() or step() re-arms."""
+    for lazy in (None, False):
+        torch.manual_seed(5)
+        model = DDP(ToyModel().cuda(), device_ids=[0], lazy_step=lazy)
+        opt = optim.Adam(model.parameters(), lr=1e-3)
+        loss = nn.MSELoss()
+        x, t = torch.randn(64, 2, device="cuda"), torch.randn(64, 1, device="cuda")
+        l1 = loss(model(x), t)
+        l1.backward()
+        with pytest.raises(NotImplementedError, match="ACCUMULATE"):
+            loss(model(x), t).backward()
+        opt.zero_grad(set_to_none=True)
+        l2 = loss(model(x), t)
+        l2.backward()
+        opt.step()
+        loss(model(x), t).backward()            # a step consumed the gradient: the next backward is fine
+        opt.step()
+        assert int(model._backend.state[0].item()) == 2
+
+
+def test_sgd_momentum_mixing_fused_and_eager_steps_matches_torch():
+    """One device-resident step counter serves the fused step (backward(); step()) and the eager one
+    (backward(); read the loss; step()): mixing them must initialise the momentum buffer exactly once.
+    Checked against torch.optim.SGD(momentum=0.9) on the same fp32 model, 1e-6 abs on the parameters
+    (lr 1e-2 bounds each update)."""
+    torch.manual_seed(9)
+    base = ToyModel()
+    import copy
+    twin = copy.deepcopy(base.layers).cuda()           # stock torch modules with the same initial values
+    model = DDP(base.cuda(), device_ids=[0])
+    opt = optim.SGD(model.parameters(), lr=1e-2, momentum=0.9)
+    opt_t = torch.optim.SGD(twin.parameters(), lr=1e-2, momentum=0.9)
+    loss = nn.MSELoss()
+    g = torch.Generator(device="cuda").manual_seed(2)
+    for it in range(8):
+        x = torch.randn(128, 2, device="cuda", generator=g)
+        t = torch.randn(128, 1, device="cuda", generator=g)
+        opt.zero_grad(set_to_none=True); opt_t.zero_grad(set_to_none=True)
+        l = loss(model(x), t)
+        l.backward()
+        if it in (0, 3, 4):                      # read before step(): gradient launch now, eager optimizer pass later
+            float(l.detach().cpu())
+        opt.step()
+        lt = torch.nn.functional.mse_loss(twin(x), t)
+        lt.backward()
+        opt_t.step()
+        assert abs(float(l.detach().cpu()) - lt.item()) <= 1e-5 * abs(lt.item()), it
+    flat_t = torch.cat([p.detach().reshape(-1) for p in twin.parameters()])
+    assert (model.flat_parameters() - flat_t).abs().max().item() <= 1e-6
+    assert int(model._backend.state[0].item()) == 8
+
+
+def test_loader_blocks_are_not_refilled_before_the_gpu_has_read_them(golden_dir):
+    """The loader cycles through 8 pinned blocks that the toy kernel reads IN PLACE; a loop that never
+    reads a loss lets the host run many iterations ahead of the GPU.  A block must not be refilled
+    until the step that reads it has run: 300 iterations without a single loss read must end exactly
+    where the loop that reads every loss ends."""
+    read_every, mx, my = _loop(300)
+    torch.manual_seed(1234)
+    ax, ay = ToyModel(), ToyModel()
+    data = ToyData()
+    model_X, model_Y = DDP(ax.cuda(), device_ids=[0]), DDP(ay.cuda(), device_ids=[0])
+    sampler = DistributedSampler(data, num_replicas=1, rank=0, shuffle=True)
+    loader = DataLoader(data, batch_size=256, shuffle=False, pin_memory=True, num_workers=0, sampler=sampler)
+    opt_X, opt_Y = optim.Adam(model_X.parameters(), lr=1e-3), optim.Adam(model_Y.parameters(), lr=1e-3)
+    loss = nn.MSELoss()
+    slow = torch.empty(64 << 20, dtype=torch.uint8, device="cuda")
+    it, epoch = 0, 0
+    while it < 300:
+        sampler.set_epoch(epoch)
+        for x, t in loader:
+            if it % 16 == 0:
+                for _ in range(20):
+                    slow.fill_(it & 0xff)            # keep the GPU far behind the host
+            opt_X.zero_grad(set_to_none=True); opt_Y.zero_grad(set_to_none=True)
+            x, t = x.cuda(), t.cuda()
+            loss(model_X(x), t).backward()
+            loss(model_Y(x), t).backward()
+            opt_X.step(); opt_Y.step()
+            it += 1
+            if it == 300:
+                break
+        epoch += 1
+    assert torch.equal(model_X.flat_parameters(), mx.flat_parameters())
+    assert torch.equal(model_Y.flat_parameters(), my.flat_parameters())
+
+
+def test_global_mean_on_one_rank_is_the_local_loss():
+    torch.manual_seed(6)
+    model = DDP(ToyModel().cuda(), device_ids=[0])
+    opt = optim.Adam(model.parameters(), lr=1e-3)
+    x, t = torch.randn(64, 2, device="cuda"), torch.randn(64, 1, device="cuda")
+    l = nn.MSELoss()(model(x), t)
+    l.backward()
+    opt.step()
+    assert float(l.detach().global_mean()) == float(l.detach().cpu())

@@ -24,9 +24,10 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _run_demo(tmp_path, world, allreduce, extra_args=("--backend=nccl", "--torchrun", "--dry_run")):
+def _run_demo(tmp_path, world, allreduce, extra_args=("--backend=nccl", "--torchrun", "--dry_run"), **extra_env):
     env = dict(os.environ, DDPB_ITERATIONS="200", DDPB_SEED="1234", DDPB_NO_WANDB="1", DDPB_ALLREDUCE=allreduce,
-               OMP_NUM_THREADS="1")
+               OMP_NUM_THREADS="1", **extra_env)
+    os.makedirs(tmp_path, exist_ok=True)
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
            "--master-addr", "127.0.0.1", "--master-port", str(_free_port()),
            os.path.join(ROOT, "tests", "_demo_worker.py"), str(tmp_path)] + list(extra_args)
@@ -54,6 +55,48 @@ def test_demo_matches_reference_run(tmp_path, golden_dir, world, allreduce):
     assert np.max(np.abs(ranks[0]["px"] - g["mid_X"])) <= 2e-5 and np.max(np.abs(ranks[0]["py"] - g["mid_Y"])) <= 2e-5
     for r in ranks[1:]:
         assert np.array_equal(r["px"], ranks[0]["px"]) and np.array_equal(r["py"], ranks[0]["py"])
+
+
+def _check_against_reference_run(ranks, g):
+    ref = np.stack([g["lossX"], g["lossY"]], axis=1)[:200]
+    losses = ranks[0]["losses"]
+    assert losses.shape == (200, 2)
+    assert np.max(np.abs(losses - ref) / ref) <= 2e-5
+    assert np.max(np.abs(ranks[0]["px"] - g["mid_X"])) <= 2e-5 and np.max(np.abs(ranks[0]["py"] - g["mid_Y"])) <= 2e-5
+    for r in ranks[1:]:
+        assert np.array_equal(r["px"], ranks[0]["px"]) and np.array_equal(r["py"], ranks[0]["py"])
+
+
+@pytest.mark.parametrize("allreduce", ["p2p", "nccl"])
+@pytest.mark.parametrize("world", [2, 4])
+def test_ranks_sharing_one_gpu_match_reference_run(tmp_path, golden_dir, world, allreduce):
+    """W processes on ONE GPU (DDPB_SHARE_GPUS=1, gloo rendezvous -- NCCL refuses two ranks per device):
+    the W-rank arithmetic of demo.py without needing W GPUs.  `p2p` is the fused in-kernel exchange
+    through IPC-mapped peer windows (the processes' kernels take turns on the GPU, each polling for
+    the other's tickets); `nccl` here means "all-reduce the bucket outside the kernel, then the fused
+    average+Adam pass", with the bucket carried by the gloo group.  Same golden fixtures, same
+    tolerances as the one-GPU-per-rank test above."""
+    ranks = _run_demo(tmp_path, world, allreduce, ("--backend=gloo", "--torchrun", "--dry_run"), DDPB_SHARE_GPUS="1",
+                      CUDA_VISIBLE_DEVICES=os.environ.get("CUDA_VISIBLE_DEVICES", "0").split(",")[0])
+    _check_against_reference_run(ranks, np.load(os.path.join(golden_dir, f"ref_w{world}.npz")))
+
+
+@pytest.mark.parametrize("allreduce", ["p2p", "nccl"])
+def test_fused_loss_equals_the_gloo_reduction(tmp_path, golden_dir, allreduce):
+    """DDPB_FUSED_LOSS=1: the logged all-rank mean loss comes out of the gradient exchange (bucket
+    element 371) one iteration late instead of two gloo all-reduces per step (demo.py:112-121).  Same
+    training trajectory, and the logged values agree with the gloo-reduced ones to 1e-6 (relative)."""
+    one_gpu = dict(DDPB_SHARE_GPUS="1", CUDA_VISIBLE_DEVICES=os.environ.get("CUDA_VISIBLE_DEVICES", "0").split(",")[0])
+    args = ("--backend=gloo", "--torchrun", "--dry_run")
+    if torch.cuda.device_count() >= 2:
+        one_gpu, args = {}, ("--backend=nccl", "--torchrun", "--dry_run")
+    gloo = _run_demo(os.path.join(tmp_path, "gloo"), 2, allreduce, args, **one_gpu)
+    fused = _run_demo(os.path.join(tmp_path, "fused"), 2, allreduce, args, DDPB_FUSED_LOSS="1", **one_gpu)
+    assert fused[0]["losses"].shape == (200, 2)
+    assert np.max(np.abs(fused[0]["losses"] - gloo[0]["losses"]) / gloo[0]["losses"]) <= 1e-6
+    for a, b in zip(gloo, fused):
+        assert np.array_equal(a["px"], b["px"]) and np.array_equal(a["py"], b["py"])
+    _check_against_reference_run(fused, np.load(os.path.join(golden_dir, "ref_w2.npz")))
 
 
 def test_single_rank_demo_entry_point(tmp_path, golden_dir):
@@ -169,18 +212,22 @@ def test_widened_model_fused_exchange_more_ranks(tmp_path, world):
     _widened_run(tmp_path, world, 0.05, "p2p")
 
 
+@pytest.mark.parametrize("devices", [(0, 1), (0, 0)])
 @pytest.mark.parametrize("mode", [1, 0])
-def test_bucket_reduce_adam_bit_exact_against_the_oracle(oracle, native_lib, mode):
+def test_bucket_reduce_adam_bit_exact_against_the_oracle(oracle, native_lib, mode, devices):
     """ddpb_bucket_reduce_adam through the C ABI, two GPUs driven from ONE process (plain device
-    buffers as the two windows, peer access enabled): after three steps the parameters of both ranks,
+    buffers as the two windows, peer access enabled -- or both "ranks" on GPU 0, their kernels on two
+    streams, which needs no second GPU): after three steps the parameters of both ranks,
     and each rank's shard of the Adam state, are BIT-identical to the CPU oracle's `sum in rank
     order -> x 1/W -> Adam` (oracle/ddp_oracle.c), nothing outside the bucket is touched, and the
     state of the shards a rank does not own stays zero."""
     import ctypes
     from distributed_training_pytorch_b200 import _lib
-    if torch.cuda.device_count() < 2:
-        pytest.skip("needs 2 GPUs")
-    _lib.check(native_lib.ddpb_enable_peer(0, 1), "ddpb_enable_peer")
+    if devices[0] != devices[1]:
+        if torch.cuda.device_count() < 2:
+            pytest.skip("needs 2 GPUs")
+        _lib.check(native_lib.ddpb_enable_peer(0, 1), "ddpb_enable_peer")
+    streams = [torch.cuda.Stream(device=d) for d in devices]
     W, P, start, n = 2, 10007, 16, 9987                    # n % 4 == 3: the scalar tail is rank 1's
     up = lambda b: (b + 255) // 256 * 256
     grads_off = up(_lib.BUCKET_FLAGS_BYTES)
@@ -191,15 +238,16 @@ def test_bucket_reduce_adam_bit_exact_against_the_oracle(oracle, native_lib, mod
     m_ref, v_ref = np.zeros(P, np.float32), np.zeros(P, np.float32)
     win, grads, params, m, v, state, table, jobs = [], [], [], [], [], [], [], []
     for d in range(W):
-        with torch.cuda.device(d):
-            w = torch.zeros(total, dtype=torch.uint8, device=f"cuda:{d}")
+        gpu = f"cuda:{devices[d]}"
+        with torch.cuda.device(devices[d]):
+            w = torch.zeros(total, dtype=torch.uint8, device=gpu)
             win.append(w)
             grads.append(w[grads_off:grads_off + 4 * P].view(torch.float32))
             params.append(w[params_off:params_off + 4 * P].view(torch.float32))
             params[d].copy_(torch.from_numpy(p_ref))
-            m.append(torch.zeros(P, device=f"cuda:{d}")); v.append(torch.zeros(P, device=f"cuda:{d}"))
-            state.append(torch.zeros(4, dtype=torch.int64, device=f"cuda:{d}"))
-            table.append(torch.from_numpy(_lib.adam_bias_table(1e-3, 0.9, 0.999)).to(f"cuda:{d}"))
+            m.append(torch.zeros(P, device=gpu)); v.append(torch.zeros(P, device=gpu))
+            state.append(torch.zeros(4, dtype=torch.int64, device=gpu))
+            table.append(torch.from_numpy(_lib.adam_bias_table(1e-3, 0.9, 0.999)).to(gpu))
     for d in range(W):
         j = _lib.BucketJob()
         for q in range(W):
@@ -215,14 +263,14 @@ def test_bucket_reduce_adam_bit_exact_against_the_oracle(oracle, native_lib, mod
         total_g = g[0] + g[1]                                                # float32, rank order
         for d in range(W):
             grads[d].copy_(torch.from_numpy(g[d] if mode else total_g))    # mode 0: already summed in place
-        for d in range(W):
+        for d in set(devices):
             torch.cuda.synchronize(d)
         for d in range(W):                                                   # both kernels in flight: they wait for each other
-            with torch.cuda.device(d):
+            with torch.cuda.device(devices[d]):
                 jobs[d].ticket = step
-                _lib.check(native_lib.ddpb_bucket_reduce_adam(ctypes.byref(jobs[d]), torch.cuda.current_stream(d).cuda_stream),
+                _lib.check(native_lib.ddpb_bucket_reduce_adam(ctypes.byref(jobs[d]), streams[d].cuda_stream),
                            "ddpb_bucket_reduce_adam")
-        for d in range(W):
+        for d in set(devices):
             torch.cuda.synchronize(d)
         sl = slice(start, start + n)
         pb, mb, vb = p_ref[sl].copy(), m_ref[sl].copy(), v_ref[sl].copy()

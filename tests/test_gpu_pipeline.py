@@ -82,14 +82,23 @@ def test_stage_argument_errors(native_lib):
     assert b"layers" in native_lib.ddpb_last_error()
 
 
-needs_two = pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def _stage_devices(same_gpu):
+    """(dev0, dev1): two GPUs, or both stages on GPU 0 -- which is what the reference's own launcher
+    produces (interactive_job_cmds/salloc_one_model_multi_gpu_torchrun.sh:5 sets TASKS_PER_NODE=1, so
+    demo_one_model_multi_gpu.py:90-91 computes dev0 = dev1 = 0) and needs no second GPU."""
+    if same_gpu:
+        return 0, 0
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    return 0, 1
 
 
-@needs_two
-def test_two_gpu_pipeline_front_end(oracle):
+@pytest.mark.parametrize("same_gpu", [False, True])
+def test_two_gpu_pipeline_front_end(oracle, same_gpu):
     import distributed_training_pytorch_b200 as b200
+    dev0, dev1 = _stage_devices(same_gpu)
     torch.manual_seed(7)
-    model = b200.DistributedDataParallel(b200.MultiGPUModel(0, 1), device_ids=None)
+    model = b200.DistributedDataParallel(b200.MultiGPUModel(dev0, dev1), device_ids=None)
     opt = b200.optim.Adam(model.parameters(), lr=1e-3)
     loss_fn = b200.nn.MSELoss()
     p = model.flat_parameters().cpu().numpy().copy()
@@ -108,11 +117,12 @@ def test_two_gpu_pipeline_front_end(oracle):
         oracle.adam_step(p, g, m, v, step)
         assert abs(float(loss.detach().cpu()) - loss_ref) <= 1e-5 * abs(loss_ref)
     assert np.max(np.abs(model.flat_parameters().cpu().numpy() - p)) <= 1e-5
-    assert model.module.layers0[0].weight.device.index == 0 and model.module.layers1[0].weight.device.index == 1
+    assert model.module.layers0[0].weight.device.index == dev0 and model.module.layers1[0].weight.device.index == dev1
 
 
-@needs_two
-def test_model_parallel_demo_entry_point(tmp_path, oracle):
+@pytest.mark.parametrize("same_gpu", [False, True])
+def test_model_parallel_demo_entry_point(tmp_path, oracle, same_gpu):
+    _stage_devices(same_gpu)
     with socket.socket() as s:
         s.bind(("127.0.0.1", 0))
         port = s.getsockname()[1]
@@ -124,6 +134,8 @@ def test_model_parallel_demo_entry_point(tmp_path, oracle):
     env = dict(os.environ, WORLD_SIZE="1", TASKS_PER_NODE="2", SLURM_LOCALID="0", SLURM_PROCID="0",
                MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), CUDA_VISIBLE_DEVICES="0,1",
                DDPB_ITERATIONS="100", DDPB_SEED="1234", DDPB_NO_WANDB="1")
+    if same_gpu:      # the reference launcher's mapping: TASKS_PER_NODE=1 puts both stages on GPU 0
+        env.update(TASKS_PER_NODE="1", CUDA_VISIBLE_DEVICES="0", DDPB_SINGLE_GPU_STAGES="1")
     proc = subprocess.run([sys.executable, "-c", code], env=env, cwd=ROOT, capture_output=True, text=True, timeout=600)
     assert proc.returncode == 0, (proc.stdout + proc.stderr)[-4000:]
     out = np.load(os.path.join(str(tmp_path), "out.npz"))

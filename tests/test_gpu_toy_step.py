@@ -154,3 +154,107 @@ def test_argument_errors(native_lib):
     assert native_lib.ddpb_toy_step(jobs, 5, None) != 0
     assert native_lib.ddpb_toy_step(jobs, 1, None) != 0          # null params
     assert b"params" in native_lib.ddpb_last_error()
+
+
+def _launch_on(native_lib, stream, harnesses):
+    jobs = (_lib.ToyJob * _lib.MAX_JOBS)()
+    for i, h in enumerate(harnesses):
+        jobs[i] = h.job
+    _lib.check(native_lib.ddpb_toy_step(jobs, len(harnesses), stream), "ddpb_toy_step")
+
+
+def test_graph_replay_equals_eager_launches(oracle, native_lib, golden_dir):
+    """K steps captured ONCE as a CUDA graph (ddpb_graph_*) and replayed twice must leave exactly what
+    2K eager launches leave: parameters, both Adam moments, the gradient bucket, the loss ring and the
+    device-resident counters (which is what lets a replay pick the next sampler row and the next
+    bias-correction entry without new arguments) -- bit for bit, for both models of a launch."""
+    import ctypes
+    K = 12
+    d = np.load(os.path.join(golden_dir, "dataset.npz"))
+    g = np.load(os.path.join(golden_dir, "ref_w1.npz"))
+    X, Y = dev(d["x"]), dev(d["y"])
+    rows = np.stack([oracle.sampler_indices(512, 2, 0, epoch=e) for e in range(16)]).astype(np.int32)
+    idx = dev(rows, torch.int32)
+
+    def pair():
+        hs = (ToyHarness(g["init_X"], ring=32), ToyHarness(g["init_Y"], ring=32))
+        for h in hs:
+            h.bind(X, Y, _lib.MODE_STEP, idx=idx, idx_rows=16, idx_stride=256, B=256)      # row = seq % 16, chosen on the device
+        return hs
+    eager, replay = pair(), pair()
+    side = torch.cuda.Stream()
+    torch.cuda.synchronize()
+    for _ in range(2 * K):
+        _launch_on(native_lib, side.cuda_stream, eager)
+    graph = ctypes.c_void_p()
+    _lib.check(native_lib.ddpb_graph_begin(side.cuda_stream), "ddpb_graph_begin")
+    for _ in range(K):
+        _launch_on(native_lib, side.cuda_stream, replay)
+    _lib.check(native_lib.ddpb_graph_end(side.cuda_stream, ctypes.byref(graph)), "ddpb_graph_end")
+    side.synchronize()
+    assert replay[0].state.cpu().tolist() == [0, 0, 0, 0]                # capture launched nothing
+    for _ in range(2):
+        _lib.check(native_lib.ddpb_graph_launch(graph, side.cuda_stream), "ddpb_graph_launch")
+    side.synchronize()
+    _lib.check(native_lib.ddpb_graph_destroy(graph), "ddpb_graph_destroy")
+    for a, b in zip(eager, replay):
+        assert a.state.cpu().tolist() == b.state.cpu().tolist() == [2 * K, 2 * K, 0, 0]
+        for name in ("params", "m", "v", "grads", "ring"):
+            assert torch.equal(getattr(a, name), getattr(b, name)), name
+    assert not torch.equal(eager[0].params, dev(g["init_X"]))
+
+
+def test_missing_peer_times_out_loudly_and_leaves_state_untouched(native_lib, golden_dir):
+    """world = 2 but the other rank never launches: after ~2 s the kernel gives up -- it must say so
+    (state.reserved[0] = 1, the loss slot holds DDPB_LOSS_TIMEOUT_BITS) and must NOT have applied a step
+    computed from a window that never filled (parameters, moments and both counters unchanged)."""
+    g = np.load(os.path.join(golden_dir, "ref_w1.npz"))
+    rng = np.random.default_rng(11)
+    x, y = dev(rng.standard_normal((256, 2))), dev(rng.standard_normal((256, 1)))
+    windows = [torch.zeros(_lib.XCHG_WINDOW_BYTES // 4, dtype=torch.int32, device="cuda") for _ in range(2)]
+    h = ToyHarness(g["init_X"], ring=4)
+    h.bind(x, y, _lib.MODE_STEP)
+    j = h.job
+    j.world, j.rank, j.inv_world = 2, 0, 0.5
+    for p, w in enumerate(windows):
+        j.peer_data[p] = w.data_ptr()
+    h.launch()
+    torch.cuda.synchronize()
+    assert h.state.cpu().tolist() == [0, 0, 1, 0]
+    assert h.ring.cpu().numpy().view(np.uint32)[0] == _lib.LOSS_TIMEOUT_BITS
+    assert np.array_equal(h.params.cpu().numpy(), g["init_X"])
+    assert not h.m.any().item() and not h.v.any().item()
+
+
+def test_one_call_iteration_gathers_launches_and_waits(oracle, native_lib, golden_dir):
+    """ddpb_toy_iteration: host gather into pinned staging + launch (the kernel reads the pinned rows in
+    place over PCIe) + wait for the pinned loss slots, in one call; same result as the separate calls
+    on a device-resident copy of the same rows."""
+    import ctypes
+    d = np.load(os.path.join(golden_dir, "dataset.npz"))
+    g = np.load(os.path.join(golden_dir, "ref_w1.npz"))
+    B = 200
+    rows = oracle.sampler_indices(512, 2, 1, epoch=5)[:B].astype(np.int64)
+    xs, ys = np.ascontiguousarray(d["x"]), np.ascontiguousarray(d["y"])
+    stage = torch.zeros(256 * 3, dtype=torch.float32).pin_memory()
+    ring = torch.zeros(8, dtype=torch.float32).pin_memory()
+    ring.numpy().view(np.uint32)[:] = _lib.LOSS_SENTINEL
+    a, b = ToyHarness(g["init_X"]), ToyHarness(g["init_X"])
+    b.bind(dev(d["x"][rows]), dev(d["y"][rows]), _lib.MODE_STEP)
+    b.launch()
+    j = a.job
+    j.x, j.y, j.idx, j.B, j.mode = stage.data_ptr(), stage.data_ptr() + 256 * 2 * 4, None, B, _lib.MODE_STEP
+    j.loss_ring, j.loss_ring_n = ring.data_ptr(), 8
+    jobs = (_lib.ToyJob * _lib.MAX_JOBS)()
+    jobs[0] = j
+    it = _lib.ToyIter()
+    it.jobs, it.njobs, it.stream = ctypes.addressof(jobs), 1, torch.cuda.current_stream().cuda_stream
+    it.X, it.Y, it.idx, it.B, it.dx, it.dy = xs.ctypes.data, ys.ctypes.data, rows.ctypes.data, B, 2, 1
+    it.out_x, it.out_y = j.x, j.y
+    it.nwait, it.sentinel_bits, it.spin_ns = 1, _lib.LOSS_SENTINEL, 1_000_000
+    it.wait_slot[0] = ring.data_ptr()
+    _lib.check(native_lib.ddpb_toy_iteration(ctypes.addressof(it)), "ddpb_toy_iteration")
+    assert np.array_equal(stage.numpy()[:2 * B].reshape(B, 2), d["x"][rows])
+    assert it.wait_value[0] == float(ring[0]) == b.loss(0)          # already there when the call returns
+    torch.cuda.synchronize()
+    assert torch.equal(a.params, b.params) and torch.equal(a.grads, b.grads)

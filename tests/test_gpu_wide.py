@@ -173,3 +173,93 @@ def test_widened_model_gradients_and_training(H, B):
     out = model(x).tensor()                                  # eager forward, against fp32 modules with the SAME parameters
     fresh = _torch_twin(model)(x)
     assert (out - fresh).abs().max().item() <= 4e-3 * fresh.abs().max().item()
+
+
+def test_wide_loop_without_loss_reads_uses_the_right_batches():
+    """The widened step copies the loader's pinned block with an ASYNCHRONOUS H2D copy; with 8 blocks in
+    rotation and steps that take far longer to run than to enqueue, a loop that never reads a loss
+    would refill a block before its copy has run unless the loader waits for the copy's event.
+    40 iterations without reads must give bit-identical parameters to 40 iterations that read every loss."""
+    import distributed_training_pytorch_b200 as b200
+
+    def run(read):
+        torch.manual_seed(3)
+        data = b200.ToyData()
+        model = b200.DistributedDataParallel(b200.ToyModel(hidden=256).cuda(), device_ids=[0])
+        opt = b200.optim.Adam(model.parameters(), lr=1e-3)
+        sampler = b200.DistributedSampler(data, num_replicas=1, rank=0, shuffle=True)
+        loader = b200.DataLoader(data, batch_size=64, shuffle=False, pin_memory=True, num_workers=0, sampler=sampler)
+        loss_fn = b200.nn.MSELoss()
+        slow = torch.empty(64 << 20, dtype=torch.uint8, device="cuda")
+        it = 0
+        for epoch in range(5):
+            sampler.set_epoch(epoch)
+            for x, t in loader:
+                if not read and it % 8 == 0:
+                    for _ in range(20):
+                        slow.fill_(1)                 # the GPU falls behind the host
+                opt.zero_grad(set_to_none=True)
+                loss = loss_fn(model(x.cuda()), t.cuda())
+                loss.backward()
+                opt.step()
+                if read:
+                    float(loss.detach().cpu())
+                it += 1
+        return model.flat_parameters().clone()
+    assert torch.equal(run(True), run(False))
+
+
+@pytest.mark.parametrize("B,H", [(256, 4096), (200, 4096), (256, 8192)])
+def test_linear_layers_at_the_benchmarked_widths(native_lib, B, H):
+    """forward / dgrad / wgrad at the widths bench.py and DESIGN.md quote (4096 and 8192; a full batch
+    and a ragged one), against fp32 torch with TF32 off.  K = H is long here: the tf32 error of an inner
+    product grows like sqrt(K), still far inside TOL (measured ~6e-4 of the output's max)."""
+    g = torch.Generator(device="cuda").manual_seed(H + B)
+    ld = 256
+    x = torch.nn.functional.leaky_relu(torch.randn(B, H, device="cuda", generator=g), 0.01)
+    W = torch.randn(H, H, device="cuda", generator=g) / H ** 0.5
+    b = torch.randn(H, device="cuda", generator=g)
+    out, out_t = torch.full((B, H), float("nan"), device="cuda"), torch.zeros(H + 1, ld, device="cuda")
+    _lib.check(native_lib.ddpb_linear_fwd(x.data_ptr(), W.data_ptr(), b.data_ptr(), out.data_ptr(), out_t.data_ptr(),
+                                          B, H, H, ld, 1, _stream()))
+    _close(out, torch.nn.functional.leaky_relu(x @ W.t() + b, 0.01))
+    assert torch.equal(out_t[:H, :B], out.t())
+    dz = torch.randn(B, H, device="cuda", generator=g)
+    dprev, dprev_t = torch.full((B, H), float("nan"), device="cuda"), torch.zeros(H, ld, device="cuda")
+    _lib.check(native_lib.ddpb_linear_dgrad(dz.data_ptr(), W.data_ptr(), x.data_ptr(), dprev.data_ptr(), dprev_t.data_ptr(),
+                                            B, H, H, ld, _stream()))
+    _close(dprev, (dz @ W) * torch.where(x > 0, 1.0, 0.01))
+    assert torch.equal(dprev_t[:, :B], dprev.t())
+    out_t[H, :B] = 1.0
+    dW, db = torch.full((H, H), float("nan"), device="cuda"), torch.full((H,), float("nan"), device="cuda")
+    _lib.check(native_lib.ddpb_linear_wgrad(dprev_t.data_ptr(), out_t.data_ptr(), dW.data_ptr(), db.data_ptr(), B, H, H, ld,
+                                            _stream()))
+    _close(dW, dprev.t() @ out)
+    _close(db, dprev.sum(dim=0))
+
+
+@pytest.mark.parametrize("H", [1024, 4096])
+def test_widened_model_steps_at_the_benchmarked_widths(H):
+    """A handful of full training steps at H = 1024 and 4096 (B = 256) against fp32 torch modules: first
+    loss within 4e-3 (same weights), later ones within 5e-2 (two Adam runs drifting apart under tf32
+    noise), parameters bounded as in the small-width test."""
+    import distributed_training_pytorch_b200 as b200
+    torch.manual_seed(H)
+    model = b200.DistributedDataParallel(b200.ToyModel(hidden=H).cuda(), device_ids=[0])
+    twin = _torch_twin(model)
+    opt = b200.optim.Adam(model.parameters(), lr=1e-3)
+    opt_t = torch.optim.Adam(twin.parameters(), lr=1e-3)
+    loss_fn = b200.nn.MSELoss()
+    g = torch.Generator(device="cuda").manual_seed(1)
+    for it in range(6):
+        z = torch.randn(256, device="cuda", generator=g)
+        x = torch.stack([z, z], 1).contiguous()
+        y = (0.5 * torch.randn(256, device="cuda", generator=g) + z * z).view(256, 1).contiguous()
+        opt.zero_grad(set_to_none=True); opt_t.zero_grad(set_to_none=True)
+        loss = loss_fn(model(x), y); loss.backward(); opt.step()
+        lt = torch.nn.functional.mse_loss(twin(x), y); lt.backward(); opt_t.step()
+        tol = 4e-3 if it == 0 else 5e-2
+        assert abs(float(loss.detach().cpu()) - lt.item()) <= tol * abs(lt.item()), it
+    flat_t = torch.cat([p.detach().reshape(-1) for p in twin.parameters()])
+    delta = (model.flat_parameters() - flat_t).abs()
+    assert delta.max().item() <= 2 * 6 * 1e-3 and delta.mean().item() <= 5e-4

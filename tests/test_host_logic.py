@@ -26,8 +26,8 @@ def test_library_exports_every_declared_symbol(native_lib):
 
 
 def test_struct_layout_matches_header():
-    # 11 pointers + 8 int32 + 5 doubles + 16 peer pointers + 4 words, naturally aligned
-    assert ctypes.sizeof(_lib.ToyJob) == 11 * 8 + 8 * 4 + 5 * 8 + 16 * 8 + 16
+    # 12 pointers + 8 int32 + 5 doubles + 16 peer pointers + 4 words, naturally aligned
+    assert ctypes.sizeof(_lib.ToyJob) == 12 * 8 + 8 * 4 + 5 * 8 + 16 * 8 + 16
     assert ctypes.sizeof(_lib.OptState) == 32
 
 
@@ -36,7 +36,7 @@ def test_ctypes_structs_agree_with_the_c_compiler(tmp_path):
     must be what the ctypes mirrors in _lib.py say (the header is the contract, gcc is the judge)."""
     import subprocess
     structs = {"ddpb_toy_job": _lib.ToyJob, "ddpb_seg_job": _lib.SegJob, "ddpb_bucket_job": _lib.BucketJob,
-               "ddpb_opt_state": _lib.OptState}
+               "ddpb_opt_state": _lib.OptState, "ddpb_toy_iter": _lib.ToyIter}
     lines = ['#include <stdio.h>', '#include <stddef.h>', '#include "ddp_b200.h"', 'int main(void) {']
     for cname, cls in structs.items():
         lines.append(f'  printf("{cname} %zu\\n", sizeof({cname}));')
