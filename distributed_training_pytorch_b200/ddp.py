@@ -353,6 +353,9 @@ class ToyBackend:
             self.keep.append(target)
 
     def _describe(self, loss, mode):
+        eng = self.engine
+        if eng.queue and self in eng.queue:      # the job struct still describes a step that has not gone out
+            eng.flush()
         self._bind_batch(loss.output.data, loss.target)
         if mode != self._mode:
             self.job.mode = self._mode = mode
@@ -478,6 +481,8 @@ class ToyBackend:
                     if rc:
                         _lib.check(rc, "ddpb_wait_f32")
                     v = self._loss_out.value
+                    if loss.launch_no > eng.completed:
+                        eng.completed = loss.launch_no       # its kernel has run, hence every earlier launch too
                 loss.value = v
         else:
             self.unread = 0

@@ -55,6 +55,8 @@ class Engine:
         self._it_addr = ctypes.addressof(it)
         it.sentinel_bits, it.spin_ns = _lib.LOSS_SENTINEL, 200_000
         self._iteration = self.lib.ddpb_toy_iteration
+        self._it_jobs = self._it_n = self._it_loader = self._it_B = None    # what the descriptor currently holds
+        self._it_gather, self._it_nwait = False, 0
         self.pending_stage = None                          # a data._Stage whose gather rides with the next launch
         self.last_stream = None                            # stream of the most recent launch
         self._stream = None
@@ -150,7 +152,9 @@ class Engine:
             for i, model in enumerate(batch):
                 self._scratch[i] = model.job
             addr = self._scratch_addr
-        it.jobs, it.njobs = addr, n
+        if addr != self._it_jobs or n != self._it_n:       # ctypes field stores cost ~0.1 us each: only what changed
+            it.jobs, it.njobs = addr, n
+            self._it_jobs, self._it_n = addr, n
         stream = self.last_stream = self._stream or self.stream()
         self.launch_no = launch_no = self.launch_no + 1
         stage = self.pending_stage
@@ -161,20 +165,27 @@ class Engine:
             if p is not None:
                 stage.pending_idx = None
                 ld = stage.loader
-                it.X, it.Y, it.idx, it.B, it.dx, it.dy = ld.x_ptr, ld.y_ptr, p[1], stage.B, stage.dx, stage.dy
-                it.out_x, it.out_y = stage.host_x_ptr, stage.host_y_ptr
-            else:
-                it.idx = None
-        else:
-            it.idx = None
+                if ld is not self._it_loader:
+                    it.X, it.Y, it.dx, it.dy = ld.x_ptr, ld.y_ptr, stage.dx, stage.dy
+                    self._it_loader = ld
+                if stage.B != self._it_B:
+                    it.B = self._it_B = stage.B
+                it.idx, it.out_x, it.out_y = p[1], stage.host_x_ptr, stage.host_y_ptr
+                self._it_gather = True
+            elif self._it_gather:
+                it.idx, self._it_gather = None, False
+        elif self._it_gather:
+            it.idx, self._it_gather = None, False
         nwait = 0
-        if wait:
-            for model in batch:
-                loss = model.last_loss
-                if loss is not None and loss.on_host and loss.value is None:
+        for model in batch:
+            loss = model.last_loss
+            if loss is not None:
+                loss.launch_no = launch_no
+                if wait and loss.on_host and loss.value is None:
                     it.wait_slot[nwait] = model.loss_ptr + 4 * loss.slot
                     nwait += 1
-        it.nwait = nwait
+        if nwait != self._it_nwait:
+            it.nwait = self._it_nwait = nwait
         rc = self._iteration(self._it_addr)
         if rc:
             _lib.check(rc, "ddpb_toy_iteration")

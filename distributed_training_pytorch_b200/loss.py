@@ -3,6 +3,8 @@ object with .backward() and .detach().cpu().  Nothing is computed when it is bui
 mean-squared error comes out of the same fused kernel that produces the gradients."""
 import torch
 
+_Output = None          # ddp.Output, bound on first use (ddp imports this module's users)
+
 
 class MSELoss:
     def __init__(self, reduction="mean"):
@@ -10,8 +12,10 @@ class MSELoss:
             raise NotImplementedError("only reduction='mean' (the reference's nn.MSELoss()) is implemented")
 
     def __call__(self, output, target):
-        from .ddp import Output
-        if not isinstance(output, Output):
+        global _Output
+        if _Output is None:
+            from .ddp import Output as _Output
+        if type(output) is not _Output:
             raise TypeError("MSELoss expects the output of a distributed_training_pytorch_b200.DistributedDataParallel "
                             "forward; eager tensors are not supported (no PyTorch fallback)")
         return Loss(output, target)
@@ -20,7 +24,7 @@ class MSELoss:
 class Loss:
     """A scalar that exists on the device once its step has been launched."""
 
-    __slots__ = ("output", "target", "backend", "slot", "on_host", "value", "batch", "global_is_sum")
+    __slots__ = ("output", "target", "backend", "slot", "on_host", "value", "batch", "global_is_sum", "launch_no")
 
     def __init__(self, output, target):
         self.output, self.target = output, target
@@ -30,6 +34,7 @@ class Loss:
         self.value = None          # the local mean loss (Python float) once it has been read
         self.batch = 0             # local batch size of the step
         self.global_is_sum = False # the reduced value that lands on the host is the squared-error SUM
+        self.launch_no = 0         # the engine launch that carried the step (orders loader-block reuse)
 
     # -- autograd-like surface ----------------------------------------------
     def backward(self):

@@ -134,6 +134,7 @@ def test_second_backward_without_step_is_rejected():
         opt.step()
         loss(model(x), t).backward()            # a step consumed the gradient: the next backward is fine
         opt.step()
+        model.flat_parameters()                 # launches what is still only described
         assert int(model._backend.state[0].item()) == 2
 
 
