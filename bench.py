@@ -176,7 +176,9 @@ def ncu_traffic():
     page = pages[-1]
     try:
         rows = list(csv.reader(open(page)))
-        hdr, units, body = rows[0], rows[1], [r for r in rows[2:] if "toy_step_kernel" in r[hdr.index("Kernel Name")]]
+        hdr, units = rows[0], rows[1]
+        name_col = hdr.index("Kernel Name")
+        body = [r for r in rows[2:] if "toy_step_kernel" in r[name_col]]
         scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
         total = 0.0
         for name in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
