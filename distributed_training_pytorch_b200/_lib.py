@@ -98,6 +98,8 @@ _SIGNATURES = {
                                     c_double, c_double, c_double, c_double, c_int64, c_void_p]),
     "ddpb_fused_avg_adam_dev": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_float,
                                         c_double, c_double, c_double, c_void_p, c_int, c_void_p, c_int, c_void_p]),
+    "ddpb_fused_avg_adam_dev_grid": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_float,
+                                             c_double, c_double, c_double, c_void_p, c_int, c_void_p, c_int, c_int, c_void_p]),
     "ddpb_fused_avg_sgd": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_float, c_double, c_double, c_int64, c_void_p]),
     "ddpb_fused_avg_sgd_dev": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_float, c_double, c_double, c_void_p, c_int,
                                        c_void_p]),

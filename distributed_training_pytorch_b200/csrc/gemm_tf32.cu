@@ -46,6 +46,7 @@
 // tests/test_gpu_wide.py.  At B <= 256 each weight byte feeds 128 FLOP per pass, below the tf32 ridge
 // (~170 FLOP/B): the roofline is weight bytes / HBM bandwidth.
 #include "common.cuh"
+#include "gemm_pair.cuh"
 #include <cuda.h>
 #include <cstdlib>
 
@@ -445,18 +446,7 @@ EncodeTiledFn encode_tiled() {
 // 2-D fp32 tensor [rows][cols] with row pitch ld (elements); box = [box_rows][box_cols], 128B swizzle.
 int make_map(CUtensorMap *map, const float *base, long long rows, long long cols, long long ld, int box_rows, int box_cols,
              CUtensorMapSwizzle swizzle = CU_TENSOR_MAP_SWIZZLE_128B) {
-    EncodeTiledFn enc = encode_tiled();
-    if (!enc) return ddpb::fail(5, "cuTensorMapEncodeTiled is not available from this driver");
-    DDPB_REQUIRE(((uintptr_t)base & 15) == 0 && (ld * 4) % 16 == 0, "TMA operand must be 16-byte aligned with a 16-byte row pitch");
-    const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
-    const cuuint64_t strides[1] = {(cuuint64_t)ld * 4};
-    const cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
-    const cuuint32_t estr[2] = {1, 1};
-    CUresult rc = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float *>(base), dims, strides, box, estr,
-                      CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    if (rc != CUDA_SUCCESS) return ddpb::fail(3000 + (int)rc, "cuTensorMapEncodeTiled failed (CUresult %d)", (int)rc);
-    return 0;
+    return ddpb::pairgemm::cached_map(map, base, rows, cols, ld, box_rows, box_cols, (int)swizzle);
 }
 
 // The five tensor maps of one launch: operands A and B, the output tile, its transposed copy and
@@ -509,6 +499,25 @@ int launch_split(const Maps &mp, const EpiParams &ep, int M, int N, int K, cudaS
     }
 }
 
+// Which kernel family runs a layer: the CTA-pair weight-stationary kernels of gemm_pair.cu or the
+// 128 x 128 single-CTA kernels of this file.  DDPB_GEMM_KERNEL=pair|tile forces one (A/B measurements);
+// the default picks per shape from what tools/gemm_probe.py measured on B200 (B = 256, L2 flushed;
+// profiles/r02_gemm_probe.jsonl): the pair kernels halve the bytes that have to reach shared memory but
+// have few, large tiles -- they win once a layer has >= 20 neuron blocks of 256 (H >= 5120: 49 vs 77 us
+// at 5120, 59 vs 89 at 6144, 78 vs 94 at 8192) and lose a few us below that (42 vs 40 us at 4096).
+// wgrad (K = batch) differs by a few percent either way; the pair form is taken where it measured faster.
+bool use_pair_kernels(int epi, long long neurons, long long other) {
+    static int forced = -1;
+    if (forced < 0) {
+        const char *e = getenv("DDPB_GEMM_KERNEL");
+        forced = !e ? 0 : (e[0] == 't' ? 1 : e[0] == 'p' ? 2 : 0);
+    }
+    if (forced) return forced == 2;
+    const long long blocks = (neurons + 255) / 256;
+    if (epi == EPI_WGRAD) return blocks >= 16 && blocks < 32 && other >= 4096;
+    return blocks >= 20;
+}
+
 }  // namespace
 
 #ifdef DDPB_GEMM_TIMELINE
@@ -528,6 +537,8 @@ DDPB_API int ddpb_linear_fwd(const float *act_in, const float *W, const float *b
                  "ddpb_linear_fwd: bad arguments (B=%d Hin=%d Hout=%d)", B, Hin, Hout);
     DDPB_REQUIRE(!act_out_t || ld_t >= B, "ddpb_linear_fwd: transposed pitch %d < batch %d", ld_t, B);
     DDPB_REQUIRE(!act_out_t || ld_t % 4 == 0, "ddpb_linear_fwd: transposed pitch %d must be a multiple of 4", ld_t);
+    if (use_pair_kernels(EPI_FWD, Hout, Hin))
+        return ddpb::pairgemm::linear_fwd(act_in, W, bias, act_out, act_out_t, B, Hin, Hout, ld_t, apply_act, (cudaStream_t)stream);
     Maps mp;
     if (int rc = make_map(&mp.a, act_in, B, Hin, Hin, BM, BK)) return rc;
     if (int rc = make_map(&mp.b, W, Hout, Hin, Hin, 128, BK)) return rc;
@@ -545,6 +556,8 @@ DDPB_API int ddpb_linear_dgrad(const float *dz, const float *W, const float *act
                  "ddpb_linear_dgrad: bad arguments (B=%d Hin=%d Hout=%d)", B, Hin, Hout);
     DDPB_REQUIRE(!dz_prev_t || ld_t >= B, "ddpb_linear_dgrad: transposed pitch %d < batch %d", ld_t, B);
     DDPB_REQUIRE(!dz_prev_t || ld_t % 4 == 0, "ddpb_linear_dgrad: transposed pitch %d must be a multiple of 4", ld_t);
+    if (use_pair_kernels(EPI_DGRAD, Hin, Hout))
+        return ddpb::pairgemm::linear_dgrad(dz, W, act_prev, dz_prev, dz_prev_t, B, Hin, Hout, ld_t, (cudaStream_t)stream);
     Maps mp;
     if (int rc = make_map(&mp.a, dz, B, Hout, Hout, BM, BK)) return rc;               // A: [m = sample][k = out neuron]
     if (int rc = make_map(&mp.b, W, Hout, Hin, Hin, BK, 32, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B)) return rc;   // B: boxes [32 k][32 n], n contiguous
@@ -561,6 +574,8 @@ DDPB_API int ddpb_linear_wgrad(const float *dz_t, const float *act_t_ext, float 
                                int ld_t, void *stream) {
     DDPB_REQUIRE(dz_t && act_t_ext && dW && db && B >= 1 && Hin >= 32 && Hout >= 32 && Hin % 4 == 0 && ld_t % 4 == 0 && ld_t >= B,
                  "ddpb_linear_wgrad: bad arguments (B=%d Hin=%d Hout=%d ld_t=%d)", B, Hin, Hout, ld_t);
+    if (use_pair_kernels(EPI_WGRAD, Hout, Hin))
+        return ddpb::pairgemm::linear_wgrad(dz_t, act_t_ext, dW, db, B, Hin, Hout, ld_t, (cudaStream_t)stream);
     Maps mp;
     if (int rc = make_map(&mp.a, dz_t, Hout, B, ld_t, BM, BK)) return rc;             // A: [m = out neuron][k = sample]
     if (int rc = make_map(&mp.b, act_t_ext, Hin + 1, B, ld_t, 128, BK)) return rc;    // B: [n = in neuron | ones][k = sample]

@@ -139,15 +139,17 @@ __device__ __forceinline__ unsigned long long global_ns() {
     return t;
 }
 // Spin until *flag >= ticket; after ~5 s record the failure in state->reserved[0] and give up.
-__device__ __forceinline__ void wait_flag(const int *flag, int ticket, ddpb_opt_state *state) {
+// Returns false on a time-out.
+__device__ __forceinline__ bool wait_flag(const int *flag, int ticket, ddpb_opt_state *state) {
     const unsigned long long t0 = global_ns();
     while (ld_acquire_sys_i32(flag) < ticket) {
         if (global_ns() - t0 > 5000000000ull) {
             state->reserved[0] = 1;
-            break;
+            return false;
         }
         __nanosleep(100);
     }
+    return true;
 }
 
 // Flags of one window: ready[bucket][source rank], done[bucket][source rank], then a CTA counter
@@ -164,18 +166,23 @@ __global__ void __launch_bounds__(256)
 bucket_reduce_adam_kernel(const __grid_constant__ ddpb_bucket_job job) {
     const int r = job.rank, b = job.bucket_index, t = (int)job.ticket;
     BucketFlags *mine = reinterpret_cast<BucketFlags *>(job.window[r]);
-    __shared__ int s_last;
+    __shared__ int s_last, s_timeout;
+    if (threadIdx.x == 0) s_timeout = 0;
+    __syncthreads();
 
     // 1. every rank has produced this bucket (and, having got that far, no longer reads the layer's
-    //    old parameters): tell the peers that we have, wait until they all have
+    //    old parameters): tell the peers that we have, wait until they all have.  A peer that does
+    //    not show up within ~5 s: every CTA of this kernel sees the same missing flag and leaves
+    //    WITHOUT touching parameters or optimizer state (state->reserved[0] tells the host).
     if (job.mode) {
 #pragma unroll
         for (int q = 0; q < W; ++q)
             if ((int)threadIdx.x == q && q != r) {
                 if (blockIdx.x == 0) st_release_sys_i32(&reinterpret_cast<BucketFlags *>(job.window[q])->ready[b][r], t);
-                wait_flag(&mine->ready[b][q], t, job.state);
+                if (!wait_flag(&mine->ready[b][q], t, job.state)) s_timeout = 1;
             }
         __syncthreads();
+        if (s_timeout) return;
     }
 
     AdamScalars k;
@@ -270,13 +277,14 @@ bucket_reduce_adam_kernel(const __grid_constant__ ddpb_bucket_job job) {
     }
 }
 
-int stream_grid(long long n, int per_thread) {
+int stream_grid(long long n, int per_thread, int ctas_per_sm = 8) {
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     long long blocks = (n / per_thread + 255) / 256;
     if (blocks < 1) blocks = 1;
-    long long cap = (long long)sms * 8;          // 8 resident 256-thread CTAs per SM
+    if (ctas_per_sm < 1 || ctas_per_sm > 8) ctas_per_sm = 8;
+    long long cap = (long long)sms * ctas_per_sm;          // at most 8 resident 256-thread CTAs per SM
     return (int)(blocks < cap ? blocks : cap);
 }
 
@@ -297,10 +305,18 @@ DDPB_API int ddpb_fused_avg_adam(const float *bucket, float *p, float *m, float 
 DDPB_API int ddpb_fused_avg_adam_dev(const float *bucket, float *p, float *m, float *v, int64_t n, float grad_scale,
                                      double beta1, double beta2, double eps, const float *bias_table,
                                      int bias_table_n, ddpb_opt_state *state, int advance, void *stream) {
+    return ddpb_fused_avg_adam_dev_grid(bucket, p, m, v, n, grad_scale, beta1, beta2, eps, bias_table, bias_table_n, state,
+                                        advance, 8, stream);
+}
+
+DDPB_API int ddpb_fused_avg_adam_dev_grid(const float *bucket, float *p, float *m, float *v, int64_t n, float grad_scale,
+                                          double beta1, double beta2, double eps, const float *bias_table,
+                                          int bias_table_n, ddpb_opt_state *state, int advance, int ctas_per_sm,
+                                          void *stream) {
     DDPB_REQUIRE(bucket && p && m && v && n >= 0 && state && bias_table && bias_table_n >= 1,
                  "ddpb_fused_avg_adam_dev: bad arguments");
     if (n > 0) {
-        avg_adam_kernel<<<stream_grid(n, 4), 256, 0, (cudaStream_t)stream>>>(
+        avg_adam_kernel<<<stream_grid(n, 4, ctas_per_sm), 256, 0, (cudaStream_t)stream>>>(
             bucket, p, m, v, n, grad_scale, 0.0, beta1, beta2, eps, 0.0, 0.0, state,
             reinterpret_cast<const float2 *>(bias_table), bias_table_n);
         ddpb::count_launch();

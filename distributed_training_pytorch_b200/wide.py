@@ -92,9 +92,17 @@ class WideBackend:
             self.dz = [torch.empty(CAP_B, H, device=dev) for _ in range(4)]
             self.dz_t = [torch.zeros(H, ld, device=dev) for _ in range(4)]
             self.side_stream = torch.cuda.Stream(device=dev)
+            self.opt_stream = torch.cuda.Stream(device=dev)
             self.out = torch.empty(CAP_B, device=dev)
             self.dz4 = torch.empty(CAP_B, device=dev)
             self.sq = torch.empty(CAP_B, device=dev)
+        # one rank: "end" = one pass over all parameters after backward (default); "layer" = each hidden layer's
+        # Adam pass right after its wgrad, on its own stream beside the rest of backward, with a capped grid.
+        # Measured on B200 (profiles/r02_wide_adam_modes.txt): "layer" is SLOWER at every width (0.563 vs
+        # 0.548 ms at H = 4096 with 4 CTAs per SM, 0.73 ms with 1) -- the GEMMs are latency-bound and lose
+        # more to the contention than the L2-hot gradient saves -- so it stays an experiment knob.
+        self.adam_mode = os.environ.get("DDPB_WIDE_ADAM", "end")
+        self.adam_ctas = int(os.environ.get("DDPB_WIDE_ADAM_CTAS", "4"))
         self.loss_dev = torch.zeros(LOSS_RING, dtype=torch.float32, device=dev)
         self.loss_host = torch.zeros(LOSS_RING, dtype=torch.float32, pin_memory=True)
         self.loss_bits = self.loss_host.numpy().view(np.uint32)
@@ -222,6 +230,7 @@ class WideBackend:
 
     def optimizer_state_dict(self):
         m, v = self.m, self.v
+        self.check_peers()
         if self.fused_exchange:
             # each rank holds Adam state for the shards it owns and zeros elsewhere: the sum is the full state
             m, v = m.clone(), v.clone()
@@ -233,15 +242,15 @@ class WideBackend:
         self.waiting = None
         self.grads_fresh = False
 
-    def _update(self, start, n, stream, advance):
+    def _update(self, start, n, stream, advance, ctas_per_sm=8):
         """Fused average + optimizer over grads[start:start+n]."""
         h, scale = self.hyper, 1.0 / self.world
         g, p, m = self.grads.data_ptr() + 4 * start, self.params.data_ptr() + 4 * start, self.m.data_ptr() + 4 * start
         if self.opt_kind == _lib.OPT_ADAM:
-            _lib.check(self.lib.ddpb_fused_avg_adam_dev(g, p, m, self.v.data_ptr() + 4 * start, n, scale, h["betas"][0],
-                                                        h["betas"][1], h["eps"], self.bias_table.data_ptr(),
-                                                        self.bias_table.shape[0], self.state.data_ptr(), int(advance),
-                                                        stream), "ddpb_fused_avg_adam_dev")
+            _lib.check(self.lib.ddpb_fused_avg_adam_dev_grid(g, p, m, self.v.data_ptr() + 4 * start, n, scale, h["betas"][0],
+                                                             h["betas"][1], h["eps"], self.bias_table.data_ptr(),
+                                                             self.bias_table.shape[0], self.state.data_ptr(), int(advance),
+                                                             ctas_per_sm, stream), "ddpb_fused_avg_adam_dev")
         else:
             _lib.check(self.lib.ddpb_fused_avg_sgd(g, p, m, n, scale, h["lr"], h["momentum"], self.sgd_steps, stream),
                        "ddpb_fused_avg_sgd")
@@ -276,6 +285,8 @@ class WideBackend:
         stream = eng.stream()
         slot = loss.slot = self.seq % LOSS_RING
         self.seq += 1
+        if self.fused_exchange and self.seq % 256 == 0:
+            self.check_peers()                  # a timed-out bucket exchange must not go unnoticed for long
         self.loss_bits[slot] = LOSS_SENTINEL
         loss_slot = self.loss_host.data_ptr() + 4 * slot
         act, act_t, dz, dz_t = self.act, self.act_t, self.dz, self.dz_t
@@ -297,6 +308,7 @@ class WideBackend:
                                   stream), "last_bwd")
         self._layer_done(4, with_update, None)
         main, side = torch.cuda.current_stream(self.device), self.side_stream
+        per_layer = with_update and self.world == 1 and self.opt_kind == _lib.OPT_ADAM and self.adam_mode == "layer"
         cur = 0
         for l in (3, 2, 1):
             w, _ = self._w(l)
@@ -307,6 +319,14 @@ class WideBackend:
                                      dz_t[cur + 1].data_ptr(), B, H, H, ld, stream), "dgrad")
             # the bucket's update overwrites W_l: it must follow wgrad (side) AND dgrad, which reads W_l (main)
             self._layer_done(l, with_update, side)
+            if per_layer:
+                # one rank: Adam on this layer NOW, on its own stream, while its gradient is still in L2 (24
+                # instead of 32 B/param of HBM traffic) and beside the next layer's GEMMs, which leave most
+                # of the HBM bandwidth unused; a capped grid leaves thread slots for their CTAs
+                opt = self.opt_stream
+                opt.wait_stream(side)
+                opt.wait_stream(main)
+                self._update(self.off[2 * l], self.off[2 * l + 2] - self.off[2 * l], opt.cuda_stream, False, self.adam_ctas)
             cur += 1
         gw, gb = self._g(0)
         ck(lib.ddpb_wide_first_bwd(dz[cur].data_ptr(), x, idx, gw, gb, B, H, stream), "first_bwd")
@@ -317,7 +337,12 @@ class WideBackend:
             torch.cuda.current_stream(self.device).wait_stream(self.comm_stream)    # parameters are final after this
         elif with_update:
             self.sgd_steps += 1
-            self._update(0, self.P, stream, True)
+            if per_layer:                                     # the thin ends (layer 0 and layer 4), then the counter
+                main.wait_stream(self.opt_stream)
+                self._update(0, self.off[2], stream, False)
+                self._update(self.off[8], self.P - self.off[8], stream, True)
+            else:
+                self._update(0, self.P, stream, True)
         self.grads_fresh = not with_update
 
     def _layer_done(self, layer, with_update, produced_on):

@@ -263,6 +263,13 @@ int ddpb_fused_avg_adam_dev(const float *bucket, float *p, float *m, float *v, i
                             float grad_scale, double beta1, double beta2, double eps,
                             const float *bias_table, int bias_table_n,
                             ddpb_opt_state *state, int advance, void *stream);
+/* Same pass with the grid capped at `ctas_per_sm` (1..8) 256-thread CTAs per SM: a pass that runs BESIDE the
+ * backward GEMMs of other layers (its own stream) must leave thread slots for their CTAs, or the GEMM
+ * launches queue behind it; 2 per SM still keeps enough loads in flight to use the HBM bandwidth that is left. */
+int ddpb_fused_avg_adam_dev_grid(const float *bucket, float *p, float *m, float *v, int64_t n,
+                                 float grad_scale, double beta1, double beta2, double eps,
+                                 const float *bias_table, int bias_table_n,
+                                 ddpb_opt_state *state, int advance, int ctas_per_sm, void *stream);
 /* SGD with optional momentum (north_star lists it beside Adam; torch:optim/sgd.py). */
 int ddpb_fused_avg_sgd(const float *bucket, float *p, float *buf, int64_t n, float grad_scale,
                        double lr, double momentum, int64_t step, void *stream);
@@ -289,7 +296,8 @@ int ddpb_fused_avg_sgd_dev(const float *bucket, float *p, float *buf, int64_t n,
  * zeroed.  `ticket` must grow from call to call for a given bucket (the step sequence number).
  * mode 1 = reduce over the peers; mode 0 = the local gradient buffer already holds the sum
  * (ncclAllReduce ran, eager backward) and only steps 3-4 are done.  A peer that does not arrive
- * within ~5 s sets state->reserved[0] = 1 and the kernel gives up.  The optimizer counters are
+ * at step 1 within ~5 s sets state->reserved[0] = 1 and the kernel leaves without touching
+ * parameters or optimizer state; callers must look at that flag (the Python layer raises).  The optimizer counters are
  * read from `state`; with advance != 0 they are incremented after the pass (last bucket of a step). */
 #define DDPB_BUCKET_MAX 1024                                         /* buckets per model */
 #define DDPB_BUCKET_FLAGS_BYTES (2 * DDPB_BUCKET_MAX * DDPB_MAX_PEERS * 4 + DDPB_BUCKET_MAX * 4)

@@ -263,3 +263,19 @@ def test_widened_model_steps_at_the_benchmarked_widths(H):
     flat_t = torch.cat([p.detach().reshape(-1) for p in twin.parameters()])
     delta = (model.flat_parameters() - flat_t).abs()
     assert delta.max().item() <= 2 * 6 * 1e-3 and delta.mean().item() <= 5e-4
+
+
+@pytest.mark.parametrize("family", ["pair", "tile"])
+def test_both_gemm_kernel_families(family):
+    """The layers run on one of two kernel families picked per shape (csrc/gemm_tf32.cu::use_pair_kernels):
+    the cta_group::2 weight-stationary kernels of csrc/gemm_pair.cu or the 128 x 128 single-CTA kernels.
+    DDPB_GEMM_KERNEL forces one; every linear-layer test of this file must pass with either (the choice is
+    read once per process, hence the subprocess)."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    proc = subprocess.run([sys.executable, "-m", "pytest", os.path.join(root, "tests", "test_gpu_wide.py"), "-m", "gpu", "-q", "-x",
+                           "-p", "no:cacheprovider", "-k", "test_linear or benchmarked_widths or gradients_and_training"],
+                          env=dict(os.environ, DDPB_GEMM_KERNEL=family), cwd=root, capture_output=True, text=True, timeout=900)
+    assert proc.returncode == 0, (proc.stdout + proc.stderr)[-3000:]
