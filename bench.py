@@ -331,6 +331,21 @@ def wide_record(c, peaks):
     c.barrier()
     ms = c.max_over_ranks(e0.elapsed_time(e1)) / steps
     final_loss = float(last.detach().cpu())
+    weak = None
+    if c.world > 1:                      # weak scaling of the same model: every rank keeps the reference's batch of 256
+        zw = torch.randn(BATCH, device="cuda")
+        x, y = torch.stack([zw, zw], 1).contiguous(), (zw * zw).view(BATCH, 1).contiguous()
+        for _ in range(3):
+            step()
+        c.barrier()
+        e0.record()
+        for _ in range(steps):
+            step()
+        e1.record()
+        c.barrier()
+        wms = c.max_over_ranks(e0.elapsed_time(e1)) / steps
+        weak = {"local_batch": BATCH, "global_batch": BATCH * c.world, "ms_per_step": wms,
+                "value": BATCH * c.world / (wms * 1e-3), "unit": UNIT, "scaling": "weak"}
     be = model._backend
     P = be.P
     hbm = peaks["hbm_gbs"]
@@ -339,7 +354,7 @@ def wide_record(c, peaks):
            "steps": steps, "ms_per_step": ms, "value": B * c.world / (ms * 1e-3), "unit": UNIT,
            "allreduce": ("none" if c.world == 1 else "fused peer-window reduce+Adam kernel per bucket" if be.fused_exchange
                          else "ncclAllReduce + fused avg+Adam"),
-           "buckets": len(be.buckets), "loss_after": final_loss,
+           "buckets": len(be.buckets), "loss_after": final_loss, "weak": weak,
            "floors_ms": {"hbm_40B_per_param": 40.0 * P / (hbm * 1e9) * 1e3,
                          "nvlink_allreduce": (2.0 * (c.world - 1) / c.world * 4.0 * P / 900e9 * 1e3) if c.world > 1 else 0.0}}
     if c.world == 1:

@@ -110,9 +110,22 @@ class WideBackend:
         self._sync_replicas()
         # torch's default of 25 MiB costs 15 % here (each bucket pays ~20 us of launch + NCCL latency,
         # DESIGN.md section 7): when the caller names no cap, one bucket per layer
-        cap = float(os.environ.get("DDPB_BUCKET_CAP_MB", bucket_cap_mb if bucket_cap_mb else 1e12))
-        self.buckets = self._plan_buckets(cap)
+        cap = os.environ.get("DDPB_BUCKET_CAP_MB", bucket_cap_mb if bucket_cap_mb else None)
+        if cap is None:
+            # no cap named: one bucket per HIDDEN layer, the thin ends riding with their neighbours (layer 4 with
+            # layer 3, layer 0 with layer 1).  Every bucket costs ~50 us of launch skew + flag handshakes at 8
+            # ranks whatever its size (profiles/r02_bucket_diag_8gpu.txt), so two 16 KB buckets of their own were
+            # 10 % of the step.  The tag is the layer that becomes ready LAST.
+            o = self.off
+            self.buckets = [(3, o[6], self.P - o[6]), (2, o[4], o[6] - o[4]), (0, 0, o[4])]
+        else:
+            self.buckets = self._plan_buckets(float(cap))
         self.comm_stream = torch.cuda.Stream(device=dev) if self.world > 1 else None
+        # DDPB_COMM_STREAMS=2: the fused bucket kernels alternate between two communication streams, so one
+        # bucket's handshakes and tail run under the next bucket's transfers
+        self.comm_streams = [self.comm_stream]
+        if self.world > 1 and int(os.environ.get("DDPB_COMM_STREAMS", "1")) > 1:
+            self.comm_streams.append(torch.cuda.Stream(device=dev))
         self.opt_kind = self.hyper = self.m = self.v = self.bias_table = None
         self.seq = 0
         self.waiting = None
@@ -334,7 +347,10 @@ class WideBackend:
         main.wait_stream(side)
         self.keep = keep
         if self.world > 1:
-            torch.cuda.current_stream(self.device).wait_stream(self.comm_stream)    # parameters are final after this
+            for comm in self.comm_streams:
+                main.wait_stream(comm)                          # parameters are final after this
+            if with_update and self.fused_exchange and len(self.comm_streams) > 1:
+                self._update(0, 0, stream, True)                # several communication streams: advance the counter here
         elif with_update:
             self.sgd_steps += 1
             if per_layer:                                     # the thin ends (layer 0 and layer 4), then the counter
@@ -353,16 +369,21 @@ class WideBackend:
         if layer == 4:
             self.sgd_steps += int(with_update)
             self.ticket += 1
-        self.comm_stream.wait_stream(torch.cuda.current_stream(self.device))
-        if produced_on is not None:
-            self.comm_stream.wait_stream(produced_on)
-        cs = self.comm_stream.cuda_stream
         for index, (bucket_layer, start, n) in enumerate(self.buckets):
             if bucket_layer != layer:
                 continue
-            last = layer == 0 and (start + n) == self.off[2]
-            if self.fused_exchange and with_update:
-                self._fused_update(index, cs, True, last)
+            fused = self.fused_exchange and with_update
+            comm = self.comm_streams[index % len(self.comm_streams)] if fused else self.comm_stream
+            comm.wait_stream(torch.cuda.current_stream(self.device))
+            if produced_on is not None:
+                comm.wait_stream(produced_on)
+            if layer < 4:
+                comm.wait_stream(self.side_stream)       # a merged bucket also holds an earlier layer's wgrad output
+            cs = comm.cuda_stream
+            last = index == len(self.buckets) - 1
+            if fused:
+                # the step counter is advanced once, after every bucket of the step (see _run)
+                self._fused_update(index, cs, True, last and len(self.comm_streams) == 1)
                 continue
             ptr = self.grads.data_ptr() + 4 * start
             if self.backend_name == "nccl":

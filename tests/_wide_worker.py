@@ -19,7 +19,7 @@ def main():
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     torch.manual_seed(100 + rank)                 # different initial weights per rank: the wrapper must broadcast rank 0's
-    model = b200.DistributedDataParallel(b200.ToyModel(hidden=H).cuda(), device_ids=[local], bucket_cap_mb=cap)
+    model = b200.DistributedDataParallel(b200.ToyModel(hidden=H).cuda(), device_ids=[local], bucket_cap_mb=(cap or None))   # 0 = default plan
     init = model.flat_parameters().cpu().numpy().copy()
     opt = b200.optim.Adam(model.parameters(), lr=1e-3)
     loss_fn = b200.nn.MSELoss()

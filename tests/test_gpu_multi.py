@@ -139,7 +139,7 @@ def test_mpiexec_entry_point_with_the_compat_launcher(tmp_path, golden_dir):
     assert np.max(np.abs(mean - ref) / ref) <= 2e-5
 
 
-def _widened_run(tmp_path, world, cap_mb, allreduce):
+def _widened_run(tmp_path, world, cap_mb, allreduce, **extra_env):
     """The widened model trained on `world` GPUs against an fp32 PyTorch model trained on the
     concatenated batch (equal shards: the average of the shard gradients IS the gradient of the whole
     batch), within the tf32 tolerance."""
@@ -148,7 +148,7 @@ def _widened_run(tmp_path, world, cap_mb, allreduce):
            "127.0.0.1", "--master-port", str(_free_port()), os.path.join(ROOT, "tests", "_wide_worker.py"), str(tmp_path),
            str(H), str(B), str(steps), str(cap_mb)]
     proc = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=600,
-                          env=dict(os.environ, OMP_NUM_THREADS="1", DDPB_ALLREDUCE=allreduce))
+                          env=dict(os.environ, OMP_NUM_THREADS="1", DDPB_ALLREDUCE=allreduce, **extra_env))
     assert proc.returncode == 0, (proc.stdout + proc.stderr)[-4000:]
     ranks = [np.load(os.path.join(tmp_path, f"rank{r}.npz")) for r in range(world)]
     r0 = ranks[0]
@@ -201,6 +201,17 @@ def test_widened_model_data_parallel(tmp_path, cap_mb, allreduce):
         pytest.skip("needs 2 GPUs")
     r0 = _widened_run(tmp_path, 2, cap_mb, allreduce)
     assert int(r0["buckets"]) == (5 if cap_mb == 25 else 8)          # 16512-float hidden layers cut at 13104 floats
+
+
+@pytest.mark.parametrize("allreduce,streams", [("p2p", "1"), ("p2p", "2"), ("nccl", "1")])
+def test_widened_model_default_bucket_plan(tmp_path, allreduce, streams):
+    """No bucket cap named: three buckets (the thin first / last layers ride with their neighbours), on one
+    or two communication streams (DDPB_COMM_STREAMS; with two, the step counter is advanced once after all
+    buckets).  Same checks as above: broadcast, bit-identical replicas, gathered optimizer state, fp32 tracking."""
+    if 2 not in _worlds():
+        pytest.skip("needs 2 GPUs")
+    r0 = _widened_run(tmp_path, 2, 0, allreduce, DDPB_COMM_STREAMS=streams)
+    assert int(r0["buckets"]) == 3
 
 
 @pytest.mark.parametrize("world", [4, 8])

@@ -41,7 +41,7 @@ def sweep(a, world):
         B = max(1, min(a.batch, 512 // world))
         for cap in caps:
             torch.manual_seed(0)
-            model = b200.DistributedDataParallel(b200.ToyModel(hidden=H).cuda(), device_ids=[local], bucket_cap_mb=cap)
+            model = b200.DistributedDataParallel(b200.ToyModel(hidden=H).cuda(), device_ids=[local], bucket_cap_mb=(cap or None))   # 0 = the package's default plan
             opt = b200.optim.Adam(model.parameters(), lr=1e-3)
             loss_fn = b200.nn.MSELoss()
             g = torch.Generator(device="cuda").manual_seed(rank)
@@ -66,21 +66,28 @@ def sweep(a, world):
             alone = None
             be = model._backend
             if be.fused_exchange:
-                alone = []
+                # DDPB_BUCKET_DIAG: comma-separated diagnostic modes of the bucket kernel (0 = the real kernel;
+                # 1 = read the local buffer instead of the peers'; 2 = do not push parameters; 3 = both; results of
+                # modes != 0 are wrong on purpose) -- each measured in this same process
+                alone = {}
                 cs = torch.cuda.current_stream().cuda_stream
-                for index, (layer, start, n) in enumerate(be.buckets):
-                    be.bucket_jobs[index].reserved = int(os.environ.get("DDPB_BUCKET_DIAG", "0"))
-                    ts = []
-                    for rep in range(5):
-                        dist.barrier(); torch.cuda.synchronize()
-                        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                        be.ticket += 1
-                        a0.record(); be._fused_update(index, cs, True, False); a1.record(); torch.cuda.synchronize()
-                        ts.append(a0.elapsed_time(a1) * 1e3)
-                    tk = torch.tensor([sorted(ts)[2]], dtype=torch.float64)
-                    dist.all_reduce(tk, op=dist.ReduceOp.MAX, group=side)
-                    alone.append({"layer": layer, "floats": n, "us": round(float(tk), 1),
-                                  "nvlink_in_gbs": round(4.0 * n * (world - 1) / world / float(tk) / 1e3, 1)})
+                for diag in [int(v) for v in os.environ.get("DDPB_BUCKET_DIAG", "0").split(",")]:
+                    rows = []
+                    for index, (layer, start, n) in enumerate(be.buckets):
+                        be.bucket_jobs[index].reserved = diag
+                        ts = []
+                        for rep in range(5):
+                            dist.barrier(); torch.cuda.synchronize()
+                            a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                            be.ticket += 1
+                            a0.record(); be._fused_update(index, cs, True, False); a1.record(); torch.cuda.synchronize()
+                            ts.append(a0.elapsed_time(a1) * 1e3)
+                        tk = torch.tensor([sorted(ts)[2]], dtype=torch.float64)
+                        dist.all_reduce(tk, op=dist.ReduceOp.MAX, group=side)
+                        rows.append({"layer": layer, "floats": n, "us": round(float(tk), 1),
+                                     "nvlink_in_gbs": round(4.0 * n * (world - 1) / world / float(tk) / 1e3, 1)})
+                        be.bucket_jobs[index].reserved = 0
+                    alone[f"diag{diag}"] = rows
             if rank == 0:
                 ms = float(t)
                 wire = 2.0 * (world - 1) / world * 4.0 * P
