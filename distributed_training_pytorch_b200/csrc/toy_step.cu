@@ -110,6 +110,18 @@ constexpr int kWeightFloats = (int)(offsetof(Smem, table) / sizeof(float));
 #define DDPB_STAMP(slot) do { } while (0)
 #endif
 
+#ifdef DDPB_XCHG_TIMELINE
+// Development aid (tools/toy_exchange_timeline.py): %globaltimer stamps (ns) of the thread that owns bucket
+// element 0, written through job.out: 0 kernel entry, 1 local gradients reduced, 2 exchange stores issued,
+// 3 every rank's ticket seen, 4 update stored, 5 = polling rounds.
+#define DDPB_XSTAMP(slot)                                                                                       \
+    do {                                                                                                        \
+        if (cta == 0 && tid == kComputeThreads && job.out) reinterpret_cast<unsigned long long *>(job.out)[slot] = global_ns(); \
+    } while (0)
+#else
+#define DDPB_XSTAMP(slot) do { } while (0)
+#endif
+
 __device__ __forceinline__ float lrelu(float z) { return z > 0.f ? z : z * kSlope; }
 
 // seq % n without a 64-bit division: a mask when n is a power of two (exact for ever), else a
@@ -277,6 +289,7 @@ toy_step_kernel(const __grid_constant__ JobList jl) {
     const int B = job.B, mode = job.mode;
     const bool compute = tid < kComputeThreads;
     DDPB_STAMP(0);
+    DDPB_XSTAMP(0);
 
     // ---- 0. every global load this kernel needs is issued before anything waits on one
     const float *__restrict__ prm = job.params;
@@ -383,6 +396,7 @@ toy_step_kernel(const __grid_constant__ JobList jl) {
         const float inv_B = __fdiv_rn(1.0f, (float)B);
         mbar_wait(&S.mbar, 0);                            // all eight CTAs have pushed their partials
         DDPB_STAMP(3);
+        DDPB_XSTAMP(1);
         const int slot = tid - kComputeThreads;
         float total = 0.f;
         if (owner) {
@@ -408,6 +422,7 @@ toy_step_kernel(const __grid_constant__ JobList jl) {
                 const size_t at = (size_t)(par * DDPB_MAX_PEERS + me) * kXchgRow + own;
                 for (int dst = 0; dst < W; ++dst)
                     st_slot_sys(reinterpret_cast<uint2 *>(jref.peer_data[dst]) + at, make_uint2(__float_as_uint(contrib), xseq));
+                DDPB_XSTAMP(2);
                 const uint2 *mine = reinterpret_cast<const uint2 *>(jref.peer_data[me]) + (size_t)(par * DDPB_MAX_PEERS) * kXchgRow + own;
                 // All W slots are polled together: the loads of one round are in flight at the same
                 // time (one NVLink/L2 round trip per round, not W).  The wait is bounded by the global
@@ -433,6 +448,10 @@ toy_step_kernel(const __grid_constant__ JobList jl) {
                         else if (now - t0 > kPeerTimeoutNs) { timed_out = true; break; }
                     }
                 }
+                DDPB_XSTAMP(3);
+#ifdef DDPB_XCHG_TIMELINE
+                if (cta == 0 && tid == kComputeThreads && job.out) reinterpret_cast<unsigned long long *>(job.out)[5] = rounds;
+#endif
                 total = 0.f;
 #pragma unroll
                 for (int src = 0; src < DDPB_MAX_PEERS; ++src)
@@ -481,6 +500,7 @@ toy_step_kernel(const __grid_constant__ JobList jl) {
             if (mode == DDPB_MODE_STEP) job.state->step = step + 1;
         }
         DDPB_STAMP(4);
+        DDPB_XSTAMP(4);
         return;
     }
 
