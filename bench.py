@@ -23,6 +23,7 @@ Numbers in the JSON line (rank 0 prints exactly one):
 `--impl reference` times that CPU path as the arm the driver compares against.
 """
 import argparse
+import gc
 import json
 import os
 import socket
@@ -600,6 +601,7 @@ def ours(args):
         barrier()
         starts = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
         stops = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
+        gc.collect()                                      # no cyclic-garbage pass of the interpreter inside the timed steps
         launches0 = eng.launches
         t_begin = time.perf_counter()
         for i in range(steps):
@@ -611,11 +613,15 @@ def ours(args):
         barrier()
         windows.append((t_begin, time.perf_counter()))
         launches = eng.launches - launches0
-        ms = max_over_ranks(sum(s.elapsed_time(e) for s, e in zip(starts, stops)))
-        return ms, launches, (model_X, model_Y, sampler, loader, opts, batches)
+        per_step = sorted(s.elapsed_time(e) for s, e in zip(starts, stops))
+        ms = max_over_ranks(sum(per_step))
+        median = per_step[len(per_step) // 2]
+        stats = {"median_ms": max_over_ranks(median), "max_ms": max_over_ranks(per_step[-1]),
+                 "steps_over_5x_median": int(max_over_ranks(float(sum(1 for t in per_step if t > 5 * median))))}
+        return ms, launches, (model_X, model_Y, sampler, loader, opts, batches), stats
 
     # ---- value: strong scaling of demo.py's 512-sample epoch
-    cold_ms, launches, kept = cold_leg(DATASET, K)
+    cold_ms, launches, kept, cold_stats = cold_leg(DATASET, K)
     model_X, model_Y, sampler, loader, opts, batches = kept
 
     # ---- hot_l2: same steps back to back, straight through the C ABI as ONE captured CUDA graph
@@ -679,7 +685,7 @@ def ours(args):
     weak = None
     if world > 1:
         Kw = min(K, 500)
-        weak_ms, _, kept = cold_leg(BATCH * world, Kw)
+        weak_ms, _, kept, _ = cold_leg(BATCH * world, Kw)
         weak = {"value": Kw * BATCH * world / (weak_ms * 1e-3), "unit": UNIT, "ms_per_step": weak_ms / Kw, "steps": Kw,
                 "dataset": BATCH * world, "local_batch": BATCH, "global_batch": BATCH * world, "scaling": "weak",
                 "timing": "as `value`: CUDA events per step, L2 flushed, max over ranks"}
@@ -767,6 +773,9 @@ def ours(args):
                 "warmup": W, "ms_per_step": cold_ms / K, "higher_is_better": True, "scaling": "strong",
                 "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": workload(world),
+                "value_per_step": dict(cold_stats, note="per-step CUDA-event times of the `value` leg, max over ranks; `value` "
+                                                        "uses their SUM, so a single host stall on any rank (the peers wait for "
+                                                        "it inside the kernel) counts in full"),
                 "notes": {"timing": "CUDA events per step; L2 flushed (256 MiB fill) between timed steps; max over ranks",
                           "parallelism": f"dp{world}",
                           "allreduce": ("none (single rank)" if world == 1 else

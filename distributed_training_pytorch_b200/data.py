@@ -377,6 +377,7 @@ class DataLoader:
         self._next_stage = 0
         self._dev = None          # (x_dev, y_dev) on the device-resident path
         self._rows = None         # (epoch0, host int32 rows, device rows)
+        self._rows_next = None    # (epoch0, future of the next block's host rows)
 
     def __len__(self):
         n = len(self.sampler) if self.sampler is not None else len(self.dataset)
@@ -417,11 +418,27 @@ class DataLoader:
         epoch = self.sampler.epoch if self.sampler is not None else 0
         per_epoch = len(self.sampler) if self.sampler is not None else len(self.dataset)
         if self._rows is None or not (self._rows[0] <= epoch < self._rows[0] + self._rows[1].shape[0]):
-            if self.sampler is not None and hasattr(self.sampler, "epochs_i32"):
-                rows = self.sampler.epochs_i32(epoch, self.EPOCH_ROWS)
-            else:
-                rows = np.tile(self._indices().astype(np.int32), (1, 1))
+            rows = None
+            nxt, self._rows_next = self._rows_next, None
+            if nxt is not None and nxt[0] == epoch:
+                rows = nxt[1].result()                      # computed on the helper thread while the last block was in use
+            if rows is None:
+                if self.sampler is not None and hasattr(self.sampler, "epochs_i32"):
+                    rows = self.sampler.epochs_i32(epoch, self.EPOCH_ROWS)
+                else:
+                    rows = np.tile(self._indices().astype(np.int32), (1, 1))
             self._rows = (epoch, rows, torch.from_numpy(rows).cuda())
+        elif (self._rows_next is None and self._rows[1].shape[0] > 1 and epoch - self._rows[0] == self._rows[1].shape[0] // 2
+              and self.sampler is not None and hasattr(self.sampler, "epochs_i32")):
+            # half-way through the block: the next block's permutations (2 ms of MT19937 + Fisher-Yates for 256
+            # epochs) are computed on a helper thread, so the refresh at the block boundary is only the upload --
+            # with several ranks a long refresh on one of them is time the others spend waiting inside their step
+            pool = DistributedSampler._pool
+            if pool is None:
+                from concurrent.futures import ThreadPoolExecutor
+                pool = DistributedSampler._pool = ThreadPoolExecutor(max_workers=1, thread_name_prefix="ddpb-sampler")
+            e0 = self._rows[0] + self._rows[1].shape[0]
+            self._rows_next = (e0, pool.submit(self.sampler.epochs_i32, e0, self.EPOCH_ROWS))
         epoch0, rows, drows = self._rows
         row = epoch - epoch0 if rows.shape[0] > 1 else 0
         base = drows.data_ptr() + row * rows.shape[1] * 4

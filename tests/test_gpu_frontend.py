@@ -214,3 +214,22 @@ def test_global_mean_on_one_rank_is_the_local_loss():
     l.backward()
     opt.step()
     assert float(l.detach().global_mean()) == float(l.detach().cpu())
+
+
+def test_device_resident_index_rows_across_block_boundaries():
+    """The HBM-resident loader uploads the sampler's index rows 256 epochs at a time and computes the next
+    block on a helper thread from the middle of the current one: every batch handle of 700 consecutive epochs
+    must point at exactly DistributedSampler's indices of that epoch (bit-exact, as everywhere)."""
+    data = ToyData()
+    sampler = DistributedSampler(data, num_replicas=2, rank=1, shuffle=True)
+    loader = DataLoader(data, batch_size=256, shuffle=False, pin_memory=True, num_workers=0, sampler=sampler,
+                        device_resident=True)
+    for epoch in range(700):
+        sampler.set_epoch(epoch)
+        batches = list(loader)
+        assert len(batches) == 1
+        x, _ = batches[0]
+        rows = x.keep
+        first = (x.idx_ptr - rows.data_ptr()) // 4
+        got = rows.reshape(-1)[first:first + x.B].cpu().numpy()
+        assert np.array_equal(got, sampler.indices(epoch).astype(np.int32)), epoch
