@@ -598,11 +598,11 @@ def ours(args):
         batches = iteration_stream(sampler, loader)
         for _ in range(W):
             one_step((model_X, model_Y), opts, next(batches), None)
-        barrier()
         starts = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
         stops = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
         gc.collect()                                      # no cyclic-garbage pass of the interpreter inside the timed steps
-        launches0 = eng.launches
+        barrier()                                         # all ranks enter the timed region together (a rank that is late
+        launches0 = eng.launches                          # into step 0 is time its peers spend waiting inside the kernel)
         t_begin = time.perf_counter()
         for i in range(steps):
             flush_buf.fill_(i & 0xff)                     # evict L2 (outside the timed region)
@@ -613,11 +613,14 @@ def ours(args):
         barrier()
         windows.append((t_begin, time.perf_counter()))
         launches = eng.launches - launches0
-        per_step = sorted(s.elapsed_time(e) for s, e in zip(starts, stops))
+        raw = [s.elapsed_time(e) for s, e in zip(starts, stops)]
+        worst = max(range(steps), key=raw.__getitem__)
+        per_step = sorted(raw)
         ms = max_over_ranks(sum(per_step))
         median = per_step[len(per_step) // 2]
         stats = {"median_ms": max_over_ranks(median), "max_ms": max_over_ranks(per_step[-1]),
-                 "steps_over_5x_median": int(max_over_ranks(float(sum(1 for t in per_step if t > 5 * median))))}
+                 "steps_over_5x_median": int(max_over_ranks(float(sum(1 for t in per_step if t > 5 * median)))),
+                 "slowest_step_index_rank0": worst}
         return ms, launches, (model_X, model_Y, sampler, loader, opts, batches), stats
 
     # ---- value: strong scaling of demo.py's 512-sample epoch
