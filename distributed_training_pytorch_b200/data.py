@@ -378,6 +378,7 @@ class DataLoader:
         self._dev = None          # (x_dev, y_dev) on the device-resident path
         self._rows = None         # (epoch0, host int32 rows, device rows)
         self._rows_next = None    # (epoch0, future of the next block's host rows)
+        self._row_bufs, self._row_turn = None, 0
 
     def __len__(self):
         n = len(self.sampler) if self.sampler is not None else len(self.dataset)
@@ -427,7 +428,18 @@ class DataLoader:
                     rows = self.sampler.epochs_i32(epoch, self.EPOCH_ROWS)
                 else:
                     rows = np.tile(self._indices().astype(np.int32), (1, 1))
-            self._rows = (epoch, rows, torch.from_numpy(rows).cuda())
+            # two device buffers used in turn and never reallocated: a fresh device allocation here can cost tens of
+            # ms once peer mappings exist (the driver maps every new segment into all peers), which the other
+            # ranks would spend waiting inside their step; the block that was current is still readable by the
+            # steps in flight while the new one is filled
+            bufs = self._row_bufs
+            if bufs is None or bufs[0].shape != rows.shape:
+                bufs = self._row_bufs = [torch.empty(rows.shape, dtype=torch.int32, device="cuda") for _ in range(2)]
+                self._row_turn = 0
+            drows = bufs[self._row_turn]
+            self._row_turn ^= 1
+            drows.copy_(torch.from_numpy(rows))
+            self._rows = (epoch, rows, drows)
         elif (self._rows_next is None and self._rows[1].shape[0] > 1 and epoch - self._rows[0] == self._rows[1].shape[0] // 2
               and self.sampler is not None and hasattr(self.sampler, "epochs_i32")):
             # half-way through the block: the next block's permutations (2 ms of MT19937 + Fisher-Yates for 256
