@@ -698,8 +698,8 @@ def ours(args):
     # W > 1: the loss that is read is the one demo.py logs, the mean over all ranks -- by default out of
     # the gradient exchange (bucket element 371), and as `e2e_gloo_loss` the reference's way (local
     # loss.cpu() + two gloo all-reduces per step, demo.py:112-121).
-    def e2e_leg(read, steps):
-        model_X, model_Y, sampler, loader, opts = build(False)
+    def e2e_leg(read, steps, n_data=DATASET):
+        model_X, model_Y, sampler, loader, opts = build(False, n_data)
         batches = iteration_stream(sampler, loader)
         for _ in range(W):
             one_step((model_X, model_Y), opts, next(batches), read)
@@ -728,6 +728,13 @@ def ours(args):
         g_ms, _, _, kept2 = e2e_leg("gloo", Kg)
         e2e_gloo = {"value": Kg * gb / (g_ms * 1e-3), "unit": UNIT, "ms_per_step": g_ms / Kg, "steps": Kg,
                     "loss_reduction": "loss.detach().cpu() * B + 2 gloo all_reduce per step (reference demo.py:112-121)"}
+        del kept2
+    e2e_weak = None
+    if world > 1:                      # the same end-to-end loop with B = 256 on every rank (dataset 256 * W)
+        Kw = min(K, 500)
+        w_ms, _, _, kept2 = e2e_leg(read_mode, Kw, BATCH * world)
+        e2e_weak = {"value": Kw * BATCH * world / (w_ms * 1e-3), "unit": UNIT, "ms_per_step": w_ms / Kw, "steps": Kw,
+                    "local_batch": BATCH, "global_batch": BATCH * world, "scaling": "weak"}
         del kept2
 
     # keep the GPU busy long enough for nvidia-smi to see the clocks this workload runs at
@@ -799,6 +806,7 @@ def ours(args):
                                                "out of the gradient exchange (no host collective)",
                                       "gloo": "loss.detach().cpu() + 2 gloo all_reduce, every step"}[read_mode]},
                 "e2e_gloo_loss": e2e_gloo,
+                "e2e_weak": e2e_weak,
                 "weak": weak,
                 "gpu_launches": launches,
                 "clocks": clocks,

@@ -332,13 +332,24 @@ pair_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
                 tmem_ld32(tmem_base + ((unsigned)(q * 32) << 16) + (unsigned)(c * 32), v);
             } else {
                 const unsigned local = saddr(smem + c * kParkChunk + (q * 32 + lane) * kParkRow);
-                ld_cluster_row(map_to_rank(local, x), v);                                    // K-rank 0 first: fixed order
-#pragma unroll 1
-                for (unsigned zz = 1; zz < (unsigned)SPLIT; ++zz) {
-                    float r[32];
-                    ld_cluster_row(map_to_rank(local, x + 2u * zz), r);
+                // every K-rank's row is requested before any is added (one DSMEM round trip instead of S - 1
+                // in a row); the sum runs in ascending K-rank order, the same on every CTA
+                float r1[32], r2[32], r3[32];
+                ld_cluster_row(map_to_rank(local, x), v);
+                if (SPLIT >= 2) ld_cluster_row(map_to_rank(local, x + 2u), r1);
+                if (SPLIT >= 3) ld_cluster_row(map_to_rank(local, x + 4u), r2);
+                if (SPLIT >= 4) ld_cluster_row(map_to_rank(local, x + 6u), r3);
+                if (SPLIT >= 2) {
 #pragma unroll
-                    for (int i = 0; i < 32; ++i) v[i] += r[i];
+                    for (int i = 0; i < 32; ++i) v[i] += r1[i];
+                }
+                if (SPLIT >= 3) {
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) v[i] += r2[i];
+                }
+                if (SPLIT >= 4) {
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) v[i] += r3[i];
                 }
             }
             if (EPI == EPI_FWD) {
