@@ -296,15 +296,15 @@ def incumbent_torch(c, hidden, batch, steps, allow_tf32):
         torch.backends.cuda.matmul.allow_tf32 = prev
 
 
-def wide_record(c, peaks):
-    """BASELINE.json configs[4]: the widened toy model (hidden width 4096), local batch 256 on one GPU
+def wide_record(c, peaks, hidden=None):
+    """BASELINE.json configs[4]: the widened toy model (hidden width 4096 by default), local batch 256 on one GPU
     and 512 / W on W GPUs (demo.py's 512-sample epoch), through the front end; per-kernel medians
     (CUDA events, L2 flushed) on one GPU; the stock-PyTorch incumbent beside it."""
     import torch
 
     import distributed_training_pytorch_b200 as b200
     from distributed_training_pytorch_b200 import _lib
-    H = int(os.environ.get("DDPB_BENCH_WIDE_HIDDEN", "4096"))
+    H = hidden or int(os.environ.get("DDPB_BENCH_WIDE_HIDDEN", "4096"))
     B = BATCH if c.world == 1 else max(1, DATASET // c.world)
     steps = 30
     torch.manual_seed(0)
@@ -749,6 +749,8 @@ def ours(args):
 
     # ---- secondary configurations (extra keys; same clock sampler)
     wide = None if args.no_wide else wide_record(c, peaks)
+    # one GPU: the same record at H = 8192, where the layers run on the CTA-pair kernels (csrc/gemm_pair.cu)
+    wide_8192 = None if (args.no_wide or world > 1) else wide_record(c, peaks, 8192)
     pipeline = None if (args.no_pipeline or world < 2) else pipeline_record(c)
     barrier()
     incumbent = None
@@ -826,6 +828,7 @@ def ours(args):
                 "parity": parity,
                 "incumbent_torch_gpu": incumbent,
                 "wide": wide,
+                "wide_h8192": wide_8192,
                 "pipeline": pipeline,
                 "loss_after_bench": [float(v) for v in last] if last else None}
         emit(line)
