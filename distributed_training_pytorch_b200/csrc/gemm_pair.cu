@@ -322,6 +322,7 @@ pair_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         float *st = reinterpret_cast<float *>(wstage + 4096);                                // [32 samples][32 neurons]
         const int sw = lane & 7;
         const bool has_o = EPI == EPI_WGRAD || ep.has_t;
+        int issued = 0;                                                                      // chunks handed to the TMA engine so far
 #pragma unroll 1
         for (int j = 0; j < kMine; ++j) {
             const int c = (int)z + j * SPLIT;
@@ -363,10 +364,19 @@ pair_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
 #pragma unroll
                 for (int i = 0; i < 32; ++i) v[i] = ((bits >> i) & 1u) ? v[i] : v[i] * kSlope;
             }
-            if (j > 0) {                                                                     // the staging is about to be reused
+            if (EPI == EPI_WGRAD) {
+                // wgrad stages only the neuron-major chunk, so the warp's 8 KB hold two of them: the TMA engine
+                // drains one while the next is being written (8 chunks per tile; a single buffer serialised them)
+                so = wstage + (issued & 1) * 4096;
+                if (issued >= 2) {
+                    if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+                    __syncwarp();
+                }
+            } else if (issued > 0) {                                                         // the staging is about to be reused
                 if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
                 __syncwarp();
             }
+            ++issued;
             if (has_o) {
 #pragma unroll
                 for (int i = 0; i < 8; ++i)
