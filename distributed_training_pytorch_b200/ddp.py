@@ -207,6 +207,7 @@ class ToyBackend:
         # the mean loss over all ranks (demo.py:112-121), a by-product of the fused exchange or of the
         # bucket all-reduce: pinned ring the GPU writes / a 4-byte async copy lands in
         self.gloss_host = self.gloss_bits = None
+        self.gloss_wait, self.gloss_ptr = False, 0    # engine.flush(wait) also waits for the all-rank mean of a fused STEP
         if self.world > 1:
             self.gloss_host = torch.zeros(LOSS_RING, dtype=torch.float32, pin_memory=True)
             self.gloss_bits = self.gloss_host.numpy().view(np.uint32)
@@ -268,7 +269,7 @@ class ToyBackend:
         for r, ptr in enumerate(mapped):
             j.peer_data[r] = ptr
         j.world, j.rank, j.inv_world = self.world, self.rank, 1.0 / self.world
-        j.global_loss_ring = self.gloss_host.data_ptr()
+        j.global_loss_ring = self.gloss_ptr = self.gloss_host.data_ptr()
         self.fused_exchange = True
         self.lazy = True
 
@@ -376,6 +377,7 @@ class ToyBackend:
             if self.gloss_bits is not None:
                 self.gloss_bits[slot] = LOSS_SENTINEL
         loss.on_host = self.ring_on_host
+        self.gloss_wait = self.fused_exchange and self.ring_on_host and mode == _lib.MODE_STEP
         self.last_loss = loss
         self.seq = seq + 1
         self.grads_fresh = mode == _lib.MODE_GRAD
@@ -508,13 +510,16 @@ class ToyBackend:
                                     "losses regularly or call .cpu() for the local value")
         if not (self.fused_exchange or loss.global_is_sum):
             raise _lib.DdpB200Error("no reduced loss for this step: it took no gradient exchange (backward only)")
-        eng = self.engine
-        rc = eng.lib.ddpb_wait_f32(self.gloss_host.data_ptr() + 4 * loss.slot, LOSS_SENTINEL, LOSS_SPIN_NS, eng.last_stream,
-                                   self._loss_out_ref)
-        if rc:
-            _lib.check(rc, "ddpb_wait_f32")
         a = np.empty((), np.float32)
-        a[()] = self._loss_out.value
+        if loss.gvalue is not None:              # the call that launched the step waited for it as well
+            a[()] = loss.gvalue
+        else:
+            eng = self.engine
+            rc = eng.lib.ddpb_wait_f32(self.gloss_host.data_ptr() + 4 * loss.slot, LOSS_SENTINEL, LOSS_SPIN_NS, eng.last_stream,
+                                       self._loss_out_ref)
+            if rc:
+                _lib.check(rc, "ddpb_wait_f32")
+            a[()] = self._loss_out.value
         if loss.global_is_sum:                   # NCCL / gloo route: the all-reduced sum; the mean is formed here
             a /= np.float32(loss.batch * self.world)
         elif int(self.gloss_bits[loss.slot]) == LOSS_TIMEOUT:

@@ -184,6 +184,9 @@ class Engine:
                 if wait and loss.on_host and loss.value is None:
                     it.wait_slot[nwait] = model.loss_ptr + 4 * loss.slot
                     nwait += 1
+                    if model.gloss_wait:                 # fused exchange: the all-rank mean lands right after it
+                        it.wait_slot[nwait] = model.gloss_ptr + 4 * loss.slot
+                        nwait += 1
         if nwait != self._it_nwait:
             it.nwait = self._it_nwait = nwait
         rc = self._iteration(self._it_addr)
@@ -196,6 +199,9 @@ class Engine:
                 if loss is not None and loss.on_host and loss.value is None:
                     loss.value = it.wait_value[k]
                     k += 1
+                    if model.gloss_wait:
+                        loss.gvalue = it.wait_value[k]
+                        k += 1
             self.completed = launch_no
         for model in batch:
             model.after_launch(stream)

@@ -24,7 +24,7 @@ class MSELoss:
 class Loss:
     """A scalar that exists on the device once its step has been launched."""
 
-    __slots__ = ("output", "target", "backend", "slot", "on_host", "value", "batch", "global_is_sum", "launch_no")
+    __slots__ = ("output", "target", "backend", "slot", "on_host", "value", "gvalue", "batch", "global_is_sum", "launch_no")
 
     def __init__(self, output, target):
         self.output, self.target = output, target
@@ -32,6 +32,7 @@ class Loss:
         self.slot = None           # ring slot once described to the engine
         self.on_host = True        # whether that slot is in the pinned host ring or the HBM ring
         self.value = None          # the local mean loss (Python float) once it has been read
+        self.gvalue = None         # the all-rank mean (fused exchange), when the launch call waited for it too
         self.batch = 0             # local batch size of the step
         self.global_is_sum = False # the reduced value that lands on the host is the squared-error SUM
         self.launch_no = 0         # the engine launch that carried the step (orders loader-block reuse)
