@@ -198,3 +198,57 @@ def test_bucket_plan_covers_the_flat_gradient_in_reverse_layer_order():
         assert all(a[1] == b[0] for a, b in zip(covered, covered[1:]))           # no gaps, no overlap
         assert all(n * 4 <= max(cap * (1 << 20), 16) for _, _, n in plan)
     assert len(plan_buckets(offsets, total, 1e9)) == 5 and len(plan_buckets(offsets, total, 1)) == 3 * 5 + 2
+
+
+def test_sampler_blocks_prefetched_on_the_helper_thread_are_the_same_permutations():
+    """Walking the epochs in order (what every training loop does) makes the sampler compute the next block
+    of 64 epochs on a helper thread from the middle of the current one; across three block boundaries every
+    epoch must still be DistributedSampler's permutation, bit for bit, and jumping around must not be
+    served from a stale prefetch."""
+    s = b200.DistributedSampler(_Range(512), num_replicas=2, rank=1, shuffle=True)
+    for epoch in range(0, 200):
+        s.set_epoch(epoch)
+        assert np.array_equal(s.cached_indices(), s.indices(epoch)), epoch
+    assert getattr(s, "_next", None) is None or s._next[0] == 256      # a block ahead at most
+    for epoch in (500, 33, 97, 96, 1000):
+        s.set_epoch(epoch)
+        assert np.array_equal(s.cached_indices(), s.indices(epoch)), epoch
+
+
+def test_host_loader_gathers_lazily_and_exactly_once():
+    """The loader records WHICH rows a pinned block is to hold; the gather itself runs when the host tensor is
+    first touched (or, on the GPU path, inside the call that launches the step).  Touching a batch twice must
+    not gather twice into a block that has meanwhile been handed out again."""
+    torch.manual_seed(1)
+    data = b200.ToyData()
+    sampler = b200.DistributedSampler(data, num_replicas=1, rank=0, shuffle=True)
+    loader = b200.DataLoader(data, batch_size=128, shuffle=False, pin_memory=False, num_workers=0, sampler=sampler)
+    sampler.set_epoch(3)
+    idx = sampler.indices()
+    it = iter(loader)
+    x0, y0 = next(it)
+    assert x0.stage.pending_idx is not None                 # nothing gathered yet
+    assert x0.shape == (128, 2) and len(y0) == 128          # shapes need no gather
+    assert x0.stage.pending_idx is not None
+    first = x0.tensor.clone()
+    assert x0.stage.pending_idx is None and torch.equal(first, data.x_dense[idx[:128]])
+    assert torch.equal(y0.tensor, data.y_dense[idx[:128]])
+    x1, _ = next(it)
+    assert x1.stage is not x0.stage                         # the ring hands out another block
+    assert torch.equal(x1.tensor, data.x_dense[idx[128:256]]) and torch.equal(x0.tensor, first)
+
+
+def test_layout_device_wraps_only_when_asked(monkeypatch):
+    from distributed_training_pytorch_b200.bootstrap import Layout
+    lay = Layout(rank=5, world_size=8, local_rank=5, local_world_size=8)
+    monkeypatch.delenv("DDPB_SHARE_GPUS", raising=False)
+    assert lay.device == 5
+    monkeypatch.setenv("DDPB_SHARE_GPUS", "1")
+    monkeypatch.setattr(torch.cuda, "device_count", lambda: 2)
+    assert lay.device == 1
+
+
+def test_local_only_wrappers_ignore_the_process_group():
+    from distributed_training_pytorch_b200.ddp import LOCAL_ONLY, _world_of
+    assert _world_of(LOCAL_ONLY) == (1, 0, None)
+    assert _world_of(None) == (1, 0, None)                  # no process group initialised in this test process
