@@ -88,6 +88,7 @@ _SIGNATURES = {
     "ddpb_linear_fwd": (c_int, [c_void_p] * 5 + [c_int] * 5 + [c_void_p]),
     "ddpb_linear_dgrad": (c_int, [c_void_p] * 5 + [c_int] * 4 + [c_void_p]),
     "ddpb_linear_wgrad": (c_int, [c_void_p] * 4 + [c_int] * 4 + [c_void_p]),
+    "ddpb_linear_wgrad_adam": (c_int, [c_void_p] * 10 + [c_int] * 4 + [c_double] * 3 + [c_void_p, c_int, c_void_p, c_void_p]),
     "ddpb_wide_first_fwd": (c_int, [c_void_p] * 6 + [c_int] * 3 + [c_void_p]),
     "ddpb_wide_last_fwd": (c_int, [c_void_p] * 8 + [c_int] * 2 + [c_void_p]),
     "ddpb_wide_last_bwd": (c_int, [c_void_p] * 10 + [c_int] * 3 + [c_void_p]),

@@ -61,13 +61,15 @@ constexpr int kParkChunk = 128 * kParkRow;
 constexpr int kParkBytes = kChunks * kParkChunk;     // 147456
 constexpr int kWarpStage = 8192;                     // per epilogue warp: neuron-major chunk + sample-major chunk
 constexpr float kSlope = 0.01f;
+constexpr int kFuseWarpStage = 2 * 3 * 4096;         // fused Adam: two buffers of {p, m, v} chunks per epilogue warp
 
 template <int EPI> struct Cfg {
-    static constexpr int kStages = EPI == EPI_WGRAD ? 3 : 6;
-    static constexpr int kCtasPerSm = EPI == EPI_WGRAD ? 2 : 1;
+    static constexpr int kStages = EPI >= EPI_WGRAD ? 3 : 6;
+    static constexpr int kCtasPerSm = EPI >= EPI_WGRAD ? 2 : 1;
     static constexpr int kRing = kStages * kStageBytes;
     static constexpr int kSmemBytes = kRing + 1024 /*alignment slack*/ + 256 /*barriers*/;
-    static_assert(EPI == EPI_WGRAD || kParkBytes + 4 * kWarpStage <= kRing, "parking + staging must fit in the dead ring");
+    static_assert(EPI >= EPI_WGRAD || kParkBytes + 4 * kWarpStage <= kRing, "parking + staging must fit in the dead ring");
+    static_assert(EPI != EPI_WGRAD_ADAM || 4 * kFuseWarpStage <= kRing, "fused-Adam staging must fit in the dead ring");
     static_assert(4 * kWarpStage <= kRing, "staging must fit in the dead ring");
 };
 
@@ -192,12 +194,39 @@ __device__ __forceinline__ unsigned make_idesc(bool a_mn_major) {
     return d;
 }
 
+// What the fused wgrad + Adam epilogue needs beside the GEMM operands.
+struct AdamFuse {
+    CUtensorMap p, m, v;               // [Hout][Hin] weight views of the flat parameter / moment buffers, boxes [32][32], 128B swizzle
+    float *dW;                         // [Hout][ldw] weight gradient (still written: .grad stays valid after step())
+    float *pb, *mb, *vb;               // the layer's bias slices [Hout]
+    const float2 *bias_table;          // Adam bias corrections (see ddp_b200.h)
+    const ddpb_opt_state *state;
+    int bias_table_n, ldw;
+    float w1, b2, w2, eps;             // 1 - beta1, beta2, 1 - beta2, eps as floats (torch's op order, csrc/optim.cu)
+};
+
+// torch's _single_tensor_adam order with explicit round-to-nearest intrinsics: the same arithmetic as
+// adam_one() in optim.cu (grad_scale = 1), so the fused update is bit-identical to the separate pass.
+__device__ __forceinline__ void adam_elem(float g, float &p, float &m, float &v, float w1, float b2, float w2, float eps,
+                                          float neg_step, float bc2_sqrt) {
+    m = __fmaf_rn(w1, __fsub_rn(g, m), m);
+    v = __fadd_rn(__fmul_rn(v, b2), __fmul_rn(__fmul_rn(w2, g), g));
+    const float denom = __fadd_rn(__fdiv_rn(__fsqrt_rn(v), bc2_sqrt), eps);
+    p = __fadd_rn(p, __fmul_rn(neg_step, __fdiv_rn(m, denom)));
+}
+
+__device__ __forceinline__ void tma_load_2d(unsigned dst, const CUtensorMap *map, unsigned bar, int c0, int c1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1) : "memory");
+}
+
 template <int EPI, bool A_MN, int SPLIT>
 __global__ void __launch_bounds__(kThreads, Cfg<EPI>::kCtasPerSm)
 pair_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                  const __grid_constant__ CUtensorMap map_o /* neuron-major out [M][N]: boxes [32 m][32 n], 128B swizzle */,
                  const __grid_constant__ CUtensorMap map_t /* sample-major out [N][M]: boxes [32 n][32 m], no swizzle */,
-                 const EpiParams ep, int M, int N, int K) {
+                 const __grid_constant__ AdamFuse fuse, const EpiParams ep, int M, int N, int K) {
     using C = Cfg<EPI>;
     constexpr int kStages = C::kStages;
     constexpr int kMine = (kChunks + SPLIT - 1) / SPLIT;        // chunks this CTA reduces and finishes (c = z, z+S, ... < 8)
@@ -219,11 +248,18 @@ pair_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < 2 * kStages + 1; ++s) mbar_init(saddr(&bars[s]), 1);
+        if (EPI == EPI_WGRAD_ADAM)                                   // {p, m, v} chunk landed: [epilogue warp][buffer]
+            for (int s = 0; s < 8; ++s) mbar_init(saddr(&bars[2 * kStages + 2 + s]), 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_o) : "memory");
-        if (EPI != EPI_WGRAD) asm volatile("prefetch.tensormap [%0];" ::"l"(&map_t) : "memory");
+        if (EPI < EPI_WGRAD) asm volatile("prefetch.tensormap [%0];" ::"l"(&map_t) : "memory");
+        if (EPI == EPI_WGRAD_ADAM) {
+            asm volatile("prefetch.tensormap [%0];" ::"l"(&fuse.p) : "memory");
+            asm volatile("prefetch.tensormap [%0];" ::"l"(&fuse.m) : "memory");
+            asm volatile("prefetch.tensormap [%0];" ::"l"(&fuse.v) : "memory");
+        }
     }
     if (warp == 2) tmem_alloc_pair(saddr(tmem_slot), kTmemCols);
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -315,7 +351,88 @@ pair_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         __syncthreads();
         cluster_sync_all();                                      // every K-rank's partial tile is parked
     }
-    if (warp >= 4) {
+    if (warp >= 4 && EPI == EPI_WGRAD_ADAM) {
+        // ===== wgrad with Adam in the epilogue (one rank) =====
+        // Per warp and 32-column chunk: the {p, m, v} tiles of my 32 neurons arrive by TMA (two buffers per warp, so
+        // the next chunk's loads fly while this one is updated), the gradient comes out of TMEM, the update runs in
+        // registers in torch's op order, the new {p, m, v} leave as TMA stores from the same buffers and dW is stored
+        // straight from registers.  HBM traffic per parameter: 12 B read + 16 B written (28 instead of 32: dW is never
+        // read back), and no separate optimizer kernel for the layer.
+        unsigned char *wstage = smem + q * kFuseWarpStage;
+        const int sw = lane & 7;
+        const int nvalid = min(kChunks, (N - n_tile0 + 31) / 32);                           // chunks that exist in this tile
+        unsigned long long *lbar = bars + 2 * kStages + 2 + q * 2;
+        float neg_step, bc2_sqrt;
+        {
+            const long long step = fuse.state->step;
+            const float2 bias = fuse.bias_table[step < fuse.bias_table_n ? step : fuse.bias_table_n - 1];
+            neg_step = bias.x; bc2_sqrt = bias.y;
+        }
+        auto issue = [&](int c) {                                                           // lane 0: request chunk c's tiles
+            const unsigned bar = saddr(&lbar[c & 1]);
+            const unsigned dst = saddr(wstage + (c & 1) * 12288);
+            mbar_expect_tx(bar, 12288);
+            tma_load_2d(dst, &fuse.p, bar, n_tile0 + c * 32, m0 + q * 32);
+            tma_load_2d(dst + 4096, &fuse.m, bar, n_tile0 + c * 32, m0 + q * 32);
+            tma_load_2d(dst + 8192, &fuse.v, bar, n_tile0 + c * 32, m0 + q * 32);
+        };
+        if (lane == 0) {
+            if (nvalid > 0) issue(0);
+            if (nvalid > 1) issue(1);
+        }
+#pragma unroll 1
+        for (int c = 0; c < nvalid; ++c) {
+            const int n_c0 = n_tile0 + c * 32;
+            unsigned char *buf = wstage + (c & 1) * 12288;
+            float g[32];
+            tmem_ld32(tmem_base + ((unsigned)(q * 32) << 16) + (unsigned)(c * 32), g);
+            mbar_wait(saddr(&lbar[c & 1]), (c >> 1) & 1);
+            if (m < M) {                                                                     // dW and the bias (column Hin of the product)
+                float *drow = fuse.dW + (long long)m * fuse.ldw + n_c0;
+#pragma unroll
+                for (int i = 0; i < 8; ++i)
+                    if (n_c0 + 4 * i < ep.n_real)
+                        *reinterpret_cast<float4 *>(drow + 4 * i) = make_float4(g[4 * i], g[4 * i + 1], g[4 * i + 2], g[4 * i + 3]);
+                const int bi = ep.n_real - n_c0;
+                if (bi >= 0 && bi < 32) {
+                    float gb = 0.f;
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) gb = (i == bi) ? g[i] : gb;
+                    ep.bias_grad[m] = gb;
+                    float pb = fuse.pb[m], mb = fuse.mb[m], vb = fuse.vb[m];
+                    adam_elem(gb, pb, mb, vb, fuse.w1, fuse.b2, fuse.w2, fuse.eps, neg_step, bc2_sqrt);
+                    fuse.pb[m] = pb; fuse.mb[m] = mb; fuse.vb[m] = vb;
+                }
+            }
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {                                                    // 16-byte piece i of my row sits at i ^ (row & 7)
+                float4 *pp = reinterpret_cast<float4 *>(buf + lane * 128 + ((i ^ sw) << 4));
+                float4 *mp = reinterpret_cast<float4 *>(buf + 4096 + lane * 128 + ((i ^ sw) << 4));
+                float4 *vp = reinterpret_cast<float4 *>(buf + 8192 + lane * 128 + ((i ^ sw) << 4));
+                float4 P4 = *pp, M4 = *mp, V4 = *vp;
+                adam_elem(g[4 * i + 0], P4.x, M4.x, V4.x, fuse.w1, fuse.b2, fuse.w2, fuse.eps, neg_step, bc2_sqrt);
+                adam_elem(g[4 * i + 1], P4.y, M4.y, V4.y, fuse.w1, fuse.b2, fuse.w2, fuse.eps, neg_step, bc2_sqrt);
+                adam_elem(g[4 * i + 2], P4.z, M4.z, V4.z, fuse.w1, fuse.b2, fuse.w2, fuse.eps, neg_step, bc2_sqrt);
+                adam_elem(g[4 * i + 3], P4.w, M4.w, V4.w, fuse.w1, fuse.b2, fuse.w2, fuse.eps, neg_step, bc2_sqrt);
+                *pp = P4; *mp = M4; *vp = V4;
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) {
+                tma_store_2d(&fuse.p, saddr(buf), n_c0, m0 + q * 32);                        // rows >= M, columns >= Hin are clipped
+                tma_store_2d(&fuse.m, saddr(buf + 4096), n_c0, m0 + q * 32);
+                tma_store_2d(&fuse.v, saddr(buf + 8192), n_c0, m0 + q * 32);
+                asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                if (c + 2 < nvalid) {                                                        // this buffer takes chunk c + 2 next
+                    asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+                    issue(c + 2);
+                }
+            }
+            __syncwarp();
+        }
+        if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    } else if (warp >= 4) {
         // ===== reduce my chunks over the K-ranks, epilogue, TMA stores =====
         unsigned char *wstage = smem + (SPLIT > 1 ? kParkBytes : 0) + q * kWarpStage;
         unsigned char *so = wstage;                                                          // [32 neurons][32 samples], swizzled
@@ -493,8 +610,13 @@ namespace {
 
 struct Maps { CUtensorMap a, b, o, t; };
 
+const AdamFuse &no_fuse() {
+    static AdamFuse zero = {};
+    return zero;
+}
+
 template <int EPI, bool A_MN, int SPLIT>
-int launch(const Maps &mp, const EpiParams &ep, int M, int N, int K, cudaStream_t stream) {
+int launch(const Maps &mp, const EpiParams &ep, int M, int N, int K, cudaStream_t stream, const AdamFuse &fuse = no_fuse()) {
     static bool configured = false;
     if (!configured) {
         DDPB_CUDA(cudaFuncSetAttribute(pair_gemm_kernel<EPI, A_MN, SPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -511,7 +633,7 @@ int launch(const Maps &mp, const EpiParams &ep, int M, int N, int K, cudaStream_
     attr.val.clusterDim.x = 2; attr.val.clusterDim.y = 1; attr.val.clusterDim.z = SPLIT;
     cfg.attrs = &attr;
     cfg.numAttrs = 1;
-    DDPB_CUDA(cudaLaunchKernelEx(&cfg, pair_gemm_kernel<EPI, A_MN, SPLIT>, mp.a, mp.b, mp.o, mp.t, ep, M, N, K));
+    DDPB_CUDA(cudaLaunchKernelEx(&cfg, pair_gemm_kernel<EPI, A_MN, SPLIT>, mp.a, mp.b, mp.o, mp.t, fuse, ep, M, N, K));
     count_launch();
     return 0;
 }
@@ -597,6 +719,28 @@ int linear_wgrad(const float *dz_t, const float *act_t_ext, float *dW, float *db
     EpiParams ep = {};
     ep.bias_grad = db; ep.n_real = Hin; ep.debug = debug_bits();
     return launch<EPI_WGRAD, false, 1>(mp, ep, Hout, Hin + 1, B, stream);
+}
+
+int linear_wgrad_adam(const float *dz_t, const float *act_t_ext, float *dW, float *db, float *p, float *pb, float *m,
+                      float *mb, float *v, float *vb, int B, int Hin, int Hout, int ld_t, double beta1, double beta2,
+                      double eps, const float *bias_table, int bias_table_n, const void *state, cudaStream_t stream) {
+    Maps mp;
+    if (int rc = cached_map(&mp.a, dz_t, Hout, B, ld_t, kRows, BK, kSwz128)) return rc;
+    if (int rc = cached_map(&mp.b, act_t_ext, Hin + 1, B, ld_t, kRows, BK, kSwz128)) return rc;
+    AdamFuse fuse = {};
+    if (int rc = cached_map(&fuse.p, p, Hout, Hin, Hin, 32, 32, kSwz128)) return rc;
+    if (int rc = cached_map(&fuse.m, m, Hout, Hin, Hin, 32, 32, kSwz128)) return rc;
+    if (int rc = cached_map(&fuse.v, v, Hout, Hin, Hin, 32, 32, kSwz128)) return rc;
+    mp.o = mp.t = fuse.p;                                                                       // unused by this epilogue
+    fuse.dW = dW; fuse.ldw = Hin;
+    fuse.pb = pb; fuse.mb = mb; fuse.vb = vb;
+    fuse.bias_table = reinterpret_cast<const float2 *>(bias_table);
+    fuse.bias_table_n = bias_table_n;
+    fuse.state = static_cast<const ddpb_opt_state *>(state);
+    fuse.w1 = (float)(1.0 - beta1); fuse.b2 = (float)beta2; fuse.w2 = (float)(1.0 - beta2); fuse.eps = (float)eps;
+    EpiParams ep = {};
+    ep.bias_grad = db; ep.n_real = Hin; ep.debug = debug_bits();
+    return launch<EPI_WGRAD_ADAM, false, 1>(mp, ep, Hout, Hin + 1, B, stream, fuse);
 }
 
 // How many clusters of the forward kernel (2 x 1 x split CTAs, ~194 KB of shared memory each) the device can

@@ -6,7 +6,7 @@
 namespace ddpb {
 namespace pairgemm {
 
-enum { EPI_FWD = 0, EPI_DGRAD = 1, EPI_WGRAD = 2 };
+enum { EPI_FWD = 0, EPI_DGRAD = 1, EPI_WGRAD = 2, EPI_WGRAD_ADAM = 3 };
 
 struct EpiParams {
     const float *bias;        // FWD: [M]
@@ -31,6 +31,12 @@ int linear_dgrad(const float *dz, const float *W, const float *act_prev, float *
 int linear_wgrad(const float *dz_t, const float *act_t_ext, float *dW, float *db, int B, int Hin, int Hout, int ld_t,
                  cudaStream_t stream);
 
+// wgrad with Adam applied to the layer in the epilogue (one rank): the weight-gradient tile never makes the round trip
+// through HBM to a separate optimizer pass.  p / m / v are the layer's [Hout][Hin] weight views of the flat buffers,
+// pb / mb / vb its bias slices; the step counter is read from `state` and NOT advanced.
+int linear_wgrad_adam(const float *dz_t, const float *act_t_ext, float *dW, float *db, float *p, float *pb, float *m,
+                      float *mb, float *v, float *vb, int B, int Hin, int Hout, int ld_t, double beta1, double beta2,
+                      double eps, const float *bias_table, int bias_table_n, const void *state, cudaStream_t stream);
 int max_active_clusters(int split, int *out);
 
 }  // namespace pairgemm

@@ -584,3 +584,17 @@ DDPB_API int ddpb_linear_wgrad(const float *dz_t, const float *act_t_ext, float 
     EpiParams ep = {nullptr, db, 0, 0, Hin};
     return launch<EPI_WGRAD, false, 128, 1>(mp, ep, Hout, Hin + 1, B, (cudaStream_t)stream);
 }
+
+DDPB_API int ddpb_linear_wgrad_adam(const float *dz_t, const float *act_t_ext, float *dW, float *db, float *p, float *pb,
+                                    float *m, float *mb, float *v, float *vb, int B, int Hin, int Hout, int ld_t,
+                                    double beta1, double beta2, double eps, const float *bias_table, int bias_table_n,
+                                    const ddpb_opt_state *state, void *stream) {
+    DDPB_REQUIRE(dz_t && act_t_ext && dW && db && p && pb && m && mb && v && vb && state && bias_table && bias_table_n >= 1,
+                 "ddpb_linear_wgrad_adam: null argument");
+    DDPB_REQUIRE(B >= 1 && Hin >= 32 && Hout >= 32 && Hin % 4 == 0 && ld_t % 4 == 0 && ld_t >= B,
+                 "ddpb_linear_wgrad_adam: bad arguments (B=%d Hin=%d Hout=%d ld_t=%d)", B, Hin, Hout, ld_t);
+    DDPB_REQUIRE((((uintptr_t)p | (uintptr_t)m | (uintptr_t)v | (uintptr_t)dW) & 15u) == 0,
+                 "ddpb_linear_wgrad_adam: dW, p, m and v must be 16-byte aligned");
+    return ddpb::pairgemm::linear_wgrad_adam(dz_t, act_t_ext, dW, db, p, pb, m, mb, v, vb, B, Hin, Hout, ld_t, beta1, beta2,
+                                             eps, bias_table, bias_table_n, state, (cudaStream_t)stream);
+}

@@ -100,7 +100,9 @@ class WideBackend:
         # Adam pass right after its wgrad, on its own stream beside the rest of backward, with a capped grid.
         # Measured on B200 (profiles/r02_wide_adam_modes.txt): "layer" is SLOWER at every width (0.563 vs
         # 0.548 ms at H = 4096 with 4 CTAs per SM, 0.73 ms with 1) -- the GEMMs are latency-bound and lose
-        # more to the contention than the L2-hot gradient saves -- so it stays an experiment knob.
+        # more to the contention than the L2-hot gradient saves -- so it stays an experiment knob.  "fused" = Adam
+        # inside each hidden layer's wgrad kernel (ddpb_linear_wgrad_adam: 28 instead of 32 B/param, bit-identical
+        # results); its epilogue keeps too few bytes in flight (0.572 vs 0.544 ms at H = 4096), also a knob.
         self.adam_mode = os.environ.get("DDPB_WIDE_ADAM", "end")
         self.adam_ctas = int(os.environ.get("DDPB_WIDE_ADAM_CTAS", "4"))
         self.loss_dev = torch.zeros(LOSS_RING, dtype=torch.float32, device=dev)
@@ -323,9 +325,24 @@ class WideBackend:
         main, side = torch.cuda.current_stream(self.device), self.side_stream
         per_layer = with_update and self.world == 1 and self.opt_kind == _lib.OPT_ADAM and self.adam_mode == "layer"
         cur = 0
+        fused_adam = with_update and self.world == 1 and self.opt_kind == _lib.OPT_ADAM and self.adam_mode == "fused"
         for l in (3, 2, 1):
-            w, _ = self._w(l)
+            w, bias = self._w(l)
             gw, gb = self._g(l)
+            if fused_adam:
+                # one rank: Adam rides in the wgrad epilogue (28 instead of 32 B/param, no optimizer pass for the
+                # layer).  It overwrites W_l, so it follows dgrad(l), and runs beside dgrad(l-1) on the side stream.
+                ck(lib.ddpb_linear_dgrad(dz[cur].data_ptr(), w, act[l - 1].data_ptr(), dz[cur + 1].data_ptr(),
+                                         dz_t[cur + 1].data_ptr(), B, H, H, ld, stream), "dgrad")
+                side.wait_stream(main)
+                h, ow, ob = self.hyper, 4 * self.off[2 * l], 4 * self.off[2 * l + 1]
+                ck(lib.ddpb_linear_wgrad_adam(dz_t[cur].data_ptr(), act_t[l - 1].data_ptr(), gw, gb, w, bias,
+                                              self.m.data_ptr() + ow, self.m.data_ptr() + ob, self.v.data_ptr() + ow,
+                                              self.v.data_ptr() + ob, B, H, H, ld, h["betas"][0], h["betas"][1], h["eps"],
+                                              self.bias_table.data_ptr(), self.bias_table.shape[0], self.state.data_ptr(),
+                                              side.cuda_stream), "wgrad_adam")
+                cur += 1
+                continue
             side.wait_stream(main)                                # dz_t[cur] is complete on the main stream
             ck(lib.ddpb_linear_wgrad(dz_t[cur].data_ptr(), act_t[l - 1].data_ptr(), gw, gb, B, H, H, ld, side.cuda_stream), "wgrad")
             ck(lib.ddpb_linear_dgrad(dz[cur].data_ptr(), w, act[l - 1].data_ptr(), dz[cur + 1].data_ptr(),
@@ -353,7 +370,7 @@ class WideBackend:
                 self._update(0, 0, stream, True)                # several communication streams: advance the counter here
         elif with_update:
             self.sgd_steps += 1
-            if per_layer:                                     # the thin ends (layer 0 and layer 4), then the counter
+            if per_layer or fused_adam:                       # the thin ends (layer 0 and layer 4), then the counter
                 main.wait_stream(self.opt_stream)
                 self._update(0, self.off[2], stream, False)
                 self._update(self.off[8], self.P - self.off[8], stream, True)

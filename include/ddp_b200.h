@@ -236,6 +236,19 @@ int ddpb_linear_dgrad(const float *dz, const float *W, const float *act_prev, fl
 int ddpb_linear_wgrad(const float *dz_t, const float *act_t_ext, float *dW, float *db, int B, int Hin, int Hout,
                       int ld_t, void *stream);
 
+/* wgrad of one layer with Adam applied in its epilogue (one rank, no gradient exchange): replaces, for that layer,
+ * loss.backward()'s weight-gradient GEMM (demo.py:107,109) AND optim.Adam.step (demo.py:110-111).  The gradient tile goes
+ * from the tensor cores' accumulator through registers into the update; p / m / v ([Hout][Hin] views of the flat buffers,
+ * 16-byte aligned; pb / mb / vb = the layer's bias slices) are read and written once, dW and db are still stored (28
+ * instead of 32 B/param of HBM traffic and no optimizer launch for the layer).  Same arithmetic, bit for bit, as
+ * ddpb_linear_wgrad followed by ddpb_fused_avg_adam_dev with grad_scale 1.  The step counter is read from `state`
+ * (bias-correction row) and NOT advanced: advance it once per step, after every layer.  The caller orders this call
+ * after the dgrad that still reads the layer's old weights. */
+int ddpb_linear_wgrad_adam(const float *dz_t, const float *act_t_ext, float *dW, float *db, float *p, float *pb,
+                           float *m, float *mb, float *v, float *vb, int B, int Hin, int Hout, int ld_t,
+                           double beta1, double beta2, double eps, const float *bias_table, int bias_table_n,
+                           const ddpb_opt_state *state, void *stream);
+
 /* The thin ends of the widened model (first Linear 2->H + LeakyReLU, toy_model_and_data.py:13-14;
  * last Linear H->1, :21; nn.MSELoss and its backward, demo.py:106-109): streaming kernels, B <= 256.
  * idx (optional) gathers rows of x / y from the HBM-resident dataset. */

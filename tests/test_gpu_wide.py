@@ -279,3 +279,35 @@ def test_both_gemm_kernel_families(family):
                            "-p", "no:cacheprovider", "-k", "test_linear or benchmarked_widths or gradients_and_training"],
                           env=dict(os.environ, DDPB_GEMM_KERNEL=family), cwd=root, capture_output=True, text=True, timeout=900)
     assert proc.returncode == 0, (proc.stdout + proc.stderr)[-3000:]
+
+
+@pytest.mark.parametrize("H,B", [(256, 256), (384, 100), (4096, 256)])
+def test_adam_in_the_wgrad_epilogue_is_bit_identical_to_the_separate_pass(H, B, monkeypatch):
+    """DDPB_WIDE_ADAM=fused applies Adam to each hidden layer inside its wgrad kernel (ddpb_linear_wgrad_adam).
+    Same gradient tiles, same op order: after 5 steps parameters, both moments, the gradient bucket and the
+    step counter must equal those of the default (one Adam pass after backward) BIT FOR BIT."""
+    import distributed_training_pytorch_b200 as b200
+
+    def run(mode):
+        monkeypatch.setenv("DDPB_WIDE_ADAM", mode)
+        torch.manual_seed(11)
+        model = b200.DistributedDataParallel(b200.ToyModel(hidden=H).cuda(), device_ids=[0])
+        opt = b200.optim.Adam(model.parameters(), lr=1e-3)
+        loss_fn = b200.nn.MSELoss()
+        g = torch.Generator(device="cuda").manual_seed(5)
+        losses = []
+        for _ in range(5):
+            z = torch.randn(B, device="cuda", generator=g)
+            x, y = torch.stack([z, z], 1).contiguous(), (z * z).view(B, 1).contiguous()
+            opt.zero_grad(set_to_none=True)
+            loss = loss_fn(model(x), y)
+            loss.backward()
+            opt.step()
+            losses.append(float(loss.detach().cpu()))
+        be = model._backend
+        torch.cuda.synchronize()
+        return (model.flat_parameters().clone(), be.m.clone(), be.v.clone(), be.grads.clone(), int(be.state[0].item()), losses)
+    a, b = run("end"), run("fused")
+    assert a[4] == b[4] == 5 and a[5] == b[5]
+    for name, x, y in zip(("params", "m", "v", "grads"), a[:4], b[:4]):
+        assert torch.equal(x, y), name
