@@ -433,12 +433,14 @@ class DataLoader:
             # ranks would spend waiting inside their step; the block that was current is still readable by the
             # steps in flight while the new one is filled
             bufs = self._row_bufs
-            if bufs is None or bufs[0].shape != rows.shape:
-                bufs = self._row_bufs = [torch.empty(rows.shape, dtype=torch.int32, device="cuda") for _ in range(2)]
+            if bufs is None or bufs[0][0].shape != rows.shape:
+                bufs = self._row_bufs = [(torch.empty(rows.shape, dtype=torch.int32, device="cuda"),
+                                          torch.empty(rows.shape, dtype=torch.int32, pin_memory=True)) for _ in range(2)]
                 self._row_turn = 0
-            drows = bufs[self._row_turn]
+            drows, pinned = bufs[self._row_turn]
             self._row_turn ^= 1
-            drows.copy_(torch.from_numpy(rows))
+            pinned.numpy()[...] = rows                      # host copy into pinned staging, then an ASYNC upload on the
+            drows.copy_(pinned, non_blocking=True)          # launch stream (ordered before the steps that read the rows)
             self._rows = (epoch, rows, drows)
         elif (self._rows_next is None and self._rows[1].shape[0] > 1 and epoch - self._rows[0] == self._rows[1].shape[0] // 2
               and self.sampler is not None and hasattr(self.sampler, "epochs_i32")):
