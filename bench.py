@@ -596,14 +596,14 @@ def ours(args):
         """HBM-resident inputs, per-step events, L2 flushed between timed steps."""
         model_X, model_Y, sampler, loader, opts = build(True, n_data)
         batches = iteration_stream(sampler, loader)
-        for _ in range(W):
+        for _ in range(W - 1):                            # the W-th warm-up step follows the barrier below
             one_step((model_X, model_Y), opts, next(batches), None)
         starts = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
         stops = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
         gc.collect()                                      # no cyclic-garbage pass of the interpreter inside the timed steps
         barrier()                                         # all ranks enter the timed region together (a rank that is late
-        # into step 0 is time its peers spend waiting inside the kernel); one more untimed step after the host
-        # barrier lines the ranks up to microseconds: the gradient exchange itself makes each wait for all
+        # into step 0 is time its peers spend waiting inside the kernel); the last warm-up step runs after the host
+        # barrier and lines the ranks up to microseconds: the gradient exchange itself makes each wait for all
         one_step((model_X, model_Y), opts, next(batches), None)
         launches0 = eng.launches
         t_begin = time.perf_counter()
@@ -704,10 +704,10 @@ def ours(args):
     def e2e_leg(read, steps, n_data=DATASET):
         model_X, model_Y, sampler, loader, opts = build(False, n_data)
         batches = iteration_stream(sampler, loader)
-        for _ in range(W):
+        for _ in range(W - 1):
             one_step((model_X, model_Y), opts, next(batches), read)
         barrier()
-        one_step((model_X, model_Y), opts, next(batches), read)    # untimed: lines the ranks up after the host barrier
+        one_step((model_X, model_Y), opts, next(batches), read)    # the W-th warm-up step: lines the ranks up after the host barrier
         t_begin = time.perf_counter()
         total, wall, last = 0.0, 0.0, None
         for i in range(steps):
